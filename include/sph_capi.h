@@ -1,0 +1,191 @@
+/*
+ * sph_capi.h — C-ABI of the B200 PCISPH step (libsph_b200.so).
+ *
+ * The reference has no FFI: its boundary is the C++ class owOpenCLSolver
+ * (/root/reference/src/owOpenCLSolver.h:28-124) driven by
+ * owPhysicsFluidSimulator::simulationStep
+ * (/root/reference/src/owPhysicsFluidSimulator.cpp:79-149).  This header is the
+ * plain-C surface that sits *underneath* the drop-in C++ classes in
+ * include/ow/ — every entry point cites the reference interface it replaces.
+ *
+ * The same ABI is exported by three libraries so tests can drive them with one
+ * loader:
+ *   smoothed-particle-hydrodynamics_b200/libsph_b200.so  CUDA sm_100a (the product)
+ *   oracle/liboracle.so                                  plain-C restatement (test infrastructure)
+ *   oracle/_ref/libsphref.so                             the reference's own sphFluid.cl compiled as C++
+ *
+ * Conventions: plain pointers and sizes, caller-owned host memory, no
+ * exceptions across the boundary; every int-returning call returns 0 on
+ * success (mirrors the reference's `unsigned int err`, 0 == CL_SUCCESS) and a
+ * negative SPH_E_* otherwise, with sph_last_error() giving the text.
+ * Not thread-safe: one context per host thread (as the reference).
+ */
+#ifndef SPH_CAPI_H
+#define SPH_CAPI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPH_MAX_NEIGHBOR_COUNT 32                  /* owOpenCLConstant.h:4  */
+#define SPH_MAX_MEMBRANES_INCLUDING_SAME_PARTICLE 7 /* owOpenCLConstant.h:6  */
+#define SPH_LIQUID_PARTICLE 1                      /* owOpenCLConstant.h:8  */
+#define SPH_ELASTIC_PARTICLE 2                     /* owOpenCLConstant.h:9  */
+#define SPH_BOUNDARY_PARTICLE 3                    /* owOpenCLConstant.h:10 */
+
+enum sph_error {
+  SPH_OK = 0,
+  SPH_E_INVALID = -1,      /* bad argument / bad params                     */
+  SPH_E_NOMEM = -2,        /* host or device allocation failed             */
+  SPH_E_DEVICE = -3,       /* CUDA runtime error (text in sph_last_error)  */
+  SPH_E_UNSUPPORTED = -4,  /* buffer/stage does not exist in this config   */
+  SPH_E_SIZE = -5          /* byte count does not match the buffer         */
+};
+
+/* Everything the reference fixes at compile time in owPhysicsConstant.h /
+ * owOpenCLConstant.h / owOpenCLSolver.cpp:7-17 / owWorldSimulation.cpp:29-47,
+ * as run-time parameters.  sph_params_default() fills the header values
+ * bit-for-bit (tests assert equality against the reference headers). */
+typedef struct sph_params {
+  /* counts (globals PARTICLE_COUNT, numOfElasticP, ... owPhysicsFluidSimulator.cpp:8-20) */
+  int32_t particle_count;
+  int32_t num_elastic;          /* elastic particles occupy original indices [0, num_elastic) */
+  int32_t num_liquid;
+  int32_t num_boundary;
+  int32_t num_membranes;
+  int32_t muscle_count;         /* MUSCLE_COUNT = 100, owWorldSimulation.cpp:31 */
+  int32_t elastic_offset;       /* numOfBoundaryP*(!generateInitialConfiguration), owOpenCLSolver.cpp:435 */
+  int32_t max_iteration;        /* maxIteration = 3, owPhysicsConstant.h:76 */
+  /* box, owPhysicsConstant.h:32-37 and owOpenCLSolver.cpp:7-12 */
+  float xmin, xmax, ymin, ymax, zmin, zmax;
+  /* hash grid, owOpenCLSolver.cpp:14-17 */
+  int32_t grid_cells_x, grid_cells_y, grid_cells_z, grid_cell_count;
+  uint32_t hash_mask;           /* 0xffff in the reference, sphFluid.cl:229,377 */
+  /* physics, owPhysicsConstant.h:12-27,62-76 */
+  float h, hash_grid_cell_size, hash_grid_cell_size_inv;
+  float simulation_scale, simulation_scale_inv, r0;
+  float rho0, mass, time_step, viscosity, stiffness, damping;
+  float gravity_x, gravity_y, gravity_z;
+  float delta;                  /* calcDelta(), owPhysicsFluidSimulator.cpp:164-203 */
+  double wpoly6_coefficient;
+  double grad_wspiky_coefficient;
+  double del2_wviscosity_coefficient;
+} sph_params;
+
+/* The reference's 18 solver stages, in simulationStep order
+ * (owOpenCLSolver.h:37-59, owPhysicsFluidSimulator.cpp:88-113). */
+enum sph_stage_id {
+  SPH_STAGE_CLEAR_BUFFERS = 0,                       /* _runClearBuffers                              */
+  SPH_STAGE_HASH_PARTICLES = 1,                      /* _runHashParticles                             */
+  SPH_STAGE_SORT = 2,                                /* _runSort                                      */
+  SPH_STAGE_SORT_POST_PASS = 3,                      /* _runSortPostPass                              */
+  SPH_STAGE_INDEXX = 4,                              /* _runIndexx                                    */
+  SPH_STAGE_INDEX_POST_PASS = 5,                     /* _runIndexPostPass                             */
+  SPH_STAGE_FIND_NEIGHBORS = 6,                      /* _runFindNeighbors                             */
+  SPH_STAGE_COMPUTE_DENSITY = 7,                     /* _run_pcisph_computeDensity                    */
+  SPH_STAGE_COMPUTE_FORCES_INIT_PRESSURE = 8,        /* _run_pcisph_computeForcesAndInitPressure      */
+  SPH_STAGE_COMPUTE_ELASTIC_FORCES = 9,              /* _run_pcisph_computeElasticForces              */
+  SPH_STAGE_PREDICT_POSITIONS = 10,                  /* _run_pcisph_predictPositions                  */
+  SPH_STAGE_PREDICT_DENSITY = 11,                    /* _run_pcisph_predictDensity                    */
+  SPH_STAGE_CORRECT_PRESSURE = 12,                   /* _run_pcisph_correctPressure                   */
+  SPH_STAGE_COMPUTE_PRESSURE_FORCE_ACCELERATION = 13,/* _run_pcisph_computePressureForceAcceleration  */
+  SPH_STAGE_INTEGRATE = 14,                          /* _run_pcisph_integrate                         */
+  SPH_STAGE_CLEAR_MEMBRANE_BUFFERS = 15,             /* _run_clearMembraneBuffers                     */
+  SPH_STAGE_MEMBRANE_INTERACTION = 16,               /* _run_computeInteractionWithMembranes          */
+  SPH_STAGE_MEMBRANE_FINALIZE = 17,                  /* _run_computeInteractionWithMembranes_finalize */
+  SPH_STAGE_COUNT = 18
+};
+
+/* Device buffers of owOpenCLSolver.h:72-97, always read/written in the
+ * REFERENCE layout (sizes from owOpenCLSolver.cpp:32-44,70-86), whatever the
+ * library keeps internally. N = particle_count, G = grid_cell_count. */
+enum sph_buffer_id {
+  SPH_BUF_POSITION = 0,               /* 2N float4: [0,N) x,y,z,type (original order); [N,2N) membrane displacement */
+  SPH_BUF_VELOCITY = 1,               /* 2N float4                                                                  */
+  SPH_BUF_PARTICLE_INDEX = 2,         /* N uint2 (cellId, serialId)                                                 */
+  SPH_BUF_PARTICLE_INDEX_BACK = 3,    /* N uint                                                                     */
+  SPH_BUF_SORTED_POSITION = 4,        /* 2N float4: [0,N) sorted, w=(float)cellId; [N,2N) predicted                 */
+  SPH_BUF_SORTED_VELOCITY = 5,        /* N float4                                                                   */
+  SPH_BUF_GRID_CELL_INDEX = 6,        /* G+1 uint, -1 for empty cells                                               */
+  SPH_BUF_GRID_CELL_INDEX_FIXED_UP = 7,/* G+1 uint                                                                  */
+  SPH_BUF_NEIGHBOR_MAP = 8,           /* 32N float2 (id as float, distance in metres), sorted index                 */
+  SPH_BUF_RHO = 9,                    /* 2N float: rho(t), rho*                                                     */
+  SPH_BUF_PRESSURE = 10,              /* N float                                                                    */
+  SPH_BUF_ACCELERATION = 11,          /* 2N float4: non-pressure, pressure                                          */
+  SPH_BUF_ELASTIC_CONNECTIONS = 12,   /* 32*Ne float4                                                               */
+  SPH_BUF_MEMBRANE_DATA = 13,         /* 3*M int                                                                    */
+  SPH_BUF_PARTICLE_MEMBRANES_LIST = 14,/* 7*Ne int                                                                  */
+  SPH_BUF_MUSCLE_ACTIVATION_SIGNAL = 15,/* muscle_count float                                                       */
+  SPH_BUF_COUNT = 16
+};
+
+typedef struct sph_ctx sph_ctx;
+
+/* Fill *p with the reference's header constants and the header box
+ * (30h x 20h x 250h), counts zero.  owPhysicsConstant.h, owOpenCLSolver.cpp:7-17. */
+int sph_params_default(sph_params *p);
+
+/* Set the box to (mx*h, my*h, mz*h) exactly as `#define XMAX mx*h` would
+ * (double product, then float), and recompute the grid as owOpenCLSolver.cpp:14-17. */
+int sph_params_set_box(sph_params *p, double mx, double my, double mz);
+
+/* owOpenCLSolver::owOpenCLSolver(position_cpp, velocity_cpp, elasticConnectionsData_cpp,
+ * membraneData_cpp, particleMembranesList_cpp), owOpenCLSolver.cpp:27-92.
+ * pos4/vel4: particle_count float4 each.  elastic4: 32*num_elastic float4 or NULL.
+ * membranes3: 3*num_membranes int or NULL.  pml7: 7*num_elastic int or NULL.
+ * All inputs are copied; unlike the reference the library does NOT take
+ * ownership of pml7 (owOpenCLSolver.cpp:80 deletes it; the C++ facade does that).
+ * device: CUDA ordinal (ignored by the CPU oracles).  NULL on failure. */
+sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4,
+                    const float *elastic4, const int32_t *membranes3,
+                    const int32_t *pml7, int device);
+
+/* owOpenCLSolver::~owOpenCLSolver, owOpenCLSolver.cpp:744-748. */
+void sph_destroy(sph_ctx *ctx);
+
+/* One reference stage, synchronous on return (QUEUE_EACH_KERNEL 1,
+ * owOpenCLConstant.h:16): owOpenCLSolver::_run*, owOpenCLSolver.cpp:213-687. */
+int sph_stage(sph_ctx *ctx, int stage_id);
+
+/* The whole device part of owPhysicsFluidSimulator::simulationStep
+ * (owPhysicsFluidSimulator.cpp:88-113): neighbour search, PCISPH loop
+ * (max_iteration fixed iterations), integrate, membranes — fused kernels,
+ * asynchronous on the context's stream. Results identical to running the
+ * 18 stages in order. */
+int sph_step(sph_ctx *ctx);
+
+/* Block until all work queued on the context has finished (queue.finish()). */
+int sph_sync(sph_ctx *ctx);
+
+/* owOpenCLSolver::updateMuscleActivityData, owOpenCLSolver.cpp:738-742. */
+int sph_set_muscles(sph_ctx *ctx, const float *signal, int n);
+
+/* owOpenCLSolver::read_position_buffer / read_density_buffer /
+ * read_particleIndex_buffer (owOpenCLSolver.h:60-62) generalised to every
+ * buffer; blocking copy of the first `bytes` bytes (bytes <= buffer size). */
+int sph_read(sph_ctx *ctx, int buffer_id, void *dst, size_t bytes);
+
+/* copy_buffer_to_device (owOpenCLSolver.cpp:717-726) for the buffers a caller
+ * may legitimately overwrite: POSITION, VELOCITY (first N float4) — used to
+ * restart from a given state. */
+int sph_write(sph_ctx *ctx, int buffer_id, const void *src, size_t bytes);
+
+/* Size in bytes of a buffer in the reference layout, 0 if absent. */
+size_t sph_buffer_bytes(const sph_ctx *ctx, int buffer_id);
+
+/* Copy the parameters the context was created with. */
+int sph_get_params(const sph_ctx *ctx, sph_params *out);
+
+/* Text of the last error on this thread ("" if none). */
+const char *sph_last_error(void);
+
+/* "cuda-sm_100a" | "oracle-c" | "reference-cl-as-c++". */
+const char *sph_backend(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPH_CAPI_H */
