@@ -1,0 +1,111 @@
+"""CPU tests (-m "not gpu"): the oracle restatement is pinned against the reference.
+
+1. constants: sph_params_default() of the restatement == the reference header values
+   (digests.json holds the bytes produced by the library that includes owPhysicsConstant.h).
+2. golden digests: every buffer after every stage of step 0, and the state after later steps, equals
+   what the reference's own kernels (sphFluid.cl compiled as C++) produced — bit for bit.
+3. when oracle/_ref/libsphref.so is present: live stage-by-stage comparison on synthetic inputs too.
+"""
+import numpy as np
+import pytest
+
+import common
+from common import capi
+
+
+@pytest.fixture(scope="module")
+def O():
+    return common.oracle_lib()
+
+
+@pytest.fixture(scope="module")
+def D():
+    return common.digests()
+
+
+def test_params_match_reference_header(O, D):
+    assert O.default_params().as_bytes().hex() == D["params_default_hex"]
+    assert O.default_params(box=(36, 24, 54)).as_bytes().hex() == D["params_boxA_hex"]
+    p = O.default_params()
+    # values quoted in SURVEY.md §8a.0
+    assert (p.grid_cells_x, p.grid_cells_y, p.grid_cells_z, p.grid_cell_count) == (31, 21, 251, 163401)
+    assert p.wpoly6_coefficient == 5.2588841030246565e+46
+    assert p.grad_wspiky_coefficient == -1.4905203261883579e+32
+    assert np.float32(p.simulation_scale) == np.float32(2.02631827e-06)
+    pa = O.default_params(box=(36, 24, 54))
+    assert (pa.grid_cells_x, pa.grid_cells_y, pa.grid_cells_z, pa.grid_cell_count) == (37, 25, 55, 50875)
+
+
+def _check_against_digests(lib, cfg, dig, muscles, later_steps):
+    ctx = common.create(lib, cfg)
+    if muscles:
+        ctx.set_muscles(common.muscle_signal(0))
+    seen = {}
+    for st in common.stage_order(cfg["params"].max_iteration):
+        ctx.stage(st)
+        k = seen.get(st, 0)
+        seen[st] = k + 1
+        want = dig["step0"]["%s#%d" % (st, k)]
+        for b, hx in want.items():
+            assert common.sha(ctx.read(b)) == hx, "stage %s#%d buffer %s differs from the reference" % (st, k, b)
+    done = 1
+    for s in later_steps:
+        while done < s:
+            if muscles:
+                ctx.set_muscles(common.muscle_signal(done))
+            ctx.step()
+            done += 1
+        for b, hx in dig["later"]["after_%d_steps" % s].items():
+            assert common.sha(ctx.read(b)) == hx, "after %d steps buffer %s differs from the reference" % (s, b)
+    ctx.close()
+
+
+def test_config_a_every_stage_bit_exact(O, D):
+    _check_against_digests(O, common.config_a(O), D["configA"], False, (1, 2, 5))
+
+
+def test_worm_every_stage_bit_exact(O, D):
+    _check_against_digests(O, common.config_worm(O), D["worm"], True, (1, 2))
+
+
+def test_samples_are_plausible(D):
+    rho = np.asarray(D["configA"]["samples"]["rho_after_step0"])
+    assert np.all(rho > 100) and np.all(rho < 2000)
+
+
+@pytest.mark.skipif(common.ref_lib() is None, reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("mask", [0xffff, 0xffffffff])
+def test_live_vs_reference_synthetic(O, mask):
+    R = common.ref_lib()
+    pos, vel = common.synthetic_block(12, 10, 14, (20, 18, 40), seed=7)
+    cfg = dict(params=common.fill_counts(O.default_params(box=(10, 9, 20)), pos), position=pos, velocity=vel)
+    cfg["params"].hash_mask = mask
+    a, b = common.create(R, cfg), common.create(O, cfg)
+    for s in range(3):
+        for st in common.stage_order():
+            a.stage(st)
+            b.stage(st)
+            common.assert_same_state(a, b, tag="step %d stage %s" % (s, st))
+
+
+def test_stable_sort_order(O):
+    """Canonical order after SORT is (cell, serial) ascending — what glibc's stable qsort gives the reference."""
+    cfg = common.config_a(O)
+    ctx = common.create(O, cfg)
+    ctx.stage("HASH_PARTICLES")
+    ctx.stage("SORT")
+    pi = ctx.read("particleIndex").astype(np.int64)
+    key = pi[:, 0] * (1 << 32) + pi[:, 1]
+    assert np.all(np.diff(key) > 0)
+
+
+def test_error_paths(O):
+    cfg = common.config_a(O)
+    ctx = common.create(O, cfg)
+    with pytest.raises(capi.SphError):
+        ctx.stage(99)
+    with pytest.raises(capi.SphError):
+        ctx.write("rho", np.zeros(4, np.float32))
+    bad = O.default_params()
+    with pytest.raises(capi.SphError):
+        O.create(bad, np.zeros((0, 4), np.float32), np.zeros((0, 4), np.float32))
