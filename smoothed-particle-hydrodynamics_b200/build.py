@@ -1,0 +1,60 @@
+"""Build libsph_b200.so (CUDA sm_100a) in-tree with nvcc.
+
+Numerics flags are part of the parity contract (DESIGN.md "Numerics"):
+  -fmad=false -prec-div=true -prec-sqrt=true -ftz=false
+so every float op is a single IEEE round-to-nearest operation, as in the reference's
+-cl-opt-disable kernels.
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG, "csrc")
+INC = os.path.join(PKG, "..", "include")
+LIB = os.path.join(PKG, "libsph_b200.so")
+OBJ = os.path.join(PKG, "build")
+SOURCES = ["sph_sort.cu", "sph_neighbors.cu", "sph_pcisph.cu", "sph_membranes.cu", "sph_capi.cu"]
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+         "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
+         "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-I", CSRC, "-I", INC]
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force=False, verbose=False, ptxas_info=False):
+    os.makedirs(OBJ, exist_ok=True)
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    headers += [os.path.join(INC, "sph_capi.h"), os.path.abspath(__file__)]
+    objs, jobs = [], []
+    for s in SOURCES:
+        src = os.path.join(CSRC, s)
+        obj = os.path.join(OBJ, s.replace(".cu", ".o"))
+        objs.append(obj)
+        if force or _stale(obj, [src] + headers):
+            cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if ptxas_info else []) + ["-c", src, "-o", obj]
+            jobs.append(cmd)
+    def run(cmd):
+        if verbose:
+            print("[build]", " ".join(cmd))
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0 or ptxas_info:
+            sys.stderr.write(r.stdout + r.stderr)
+        if r.returncode != 0:
+            raise RuntimeError("nvcc failed: " + " ".join(cmd))
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        list(ex.map(run, jobs))
+    if jobs or force or _stale(LIB, objs):
+        run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart_static", "-ldl", "-lrt", "-lpthread"])
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose=True, ptxas_info="-v" in sys.argv))

@@ -1,0 +1,369 @@
+// sph_capi.cu — the C-ABI of include/sph_capi.h over the CUDA kernels (libsph_b200.so).
+//
+// Host orchestration that replaces owOpenCLSolver (owOpenCLSolver.cpp:27-92 buffers,
+// :213-687 stage launchers) and the device half of owPhysicsFluidSimulator::simulationStep
+// (owPhysicsFluidSimulator.cpp:88-113). No OpenCL, no CPU fallback: every entry point either
+// runs on the CUDA device or fails with SPH_E_DEVICE.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+
+#include "sph_ctx.h"
+
+int sph_scan_tiles_for(int n);
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+
+#define CU(call)                                                                                     \
+  do {                                                                                               \
+    cudaError_t _e = (call);                                                                         \
+    if (_e != cudaSuccess)                                                                           \
+      return fail(SPH_E_DEVICE, std::string(#call) + ": " + cudaGetErrorString(_e));                 \
+  } while (0)
+
+extern "C" {
+
+const char *sph_backend(void) { return "cuda-sm_100a"; }
+const char *sph_last_error(void) { return g_err.c_str(); }
+
+// ---------------------------------------------------------------- constants
+// owPhysicsConstant.h:12-76 and calcDelta (owPhysicsFluidSimulator.cpp:164-203), evaluated on the
+// host with the reference's expression types: pow(float,float) is powf in C++, sqrt(float) sqrtf,
+// pow(float,int) the exact double square; `beta` is an all-float (denormal) product widened last.
+static float calc_delta(float mass, float rho0, float h, float simulationScale, double beta, double gradW) {
+  static const float x[32] = {1, 1, 0, -1, -1, -1, 0, 1, 1, 1, 0, -1, -1, -1, 0, 1, 1, 1, 0, -1, -1, -1, 0, 1, 2, -2, 0, 0, 0, 0, 0, 0};
+  static const float y[32] = {0, 1, 1, 1, 0, -1, -1, -1, 0, 1, 1, 1, 0, -1, -1, -1, 0, 1, 1, 1, 0, -1, -1, -1, 0, 0, 2, -2, 0, 0, 0, 0};
+  static const float z[32] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1, 1, 1, -1, -1, -1, -1, -1, -1, -1, -1, 0, 0, 0, 0, 2, -2, 1, -1};
+  float s1x = 0.f, s1y = 0.f, s1z = 0.f;
+  double sum2 = 0.0;
+  const float particleRadius = powf(mass / rho0, 1.f / 3.f);
+  for (int i = 0; i < 32; i++) {
+    float vx = x[i] * 0.8f * particleRadius, vy = y[i] * 0.8f * particleRadius, vz = z[i] * 0.8f * particleRadius;
+    float dist = sqrtf(vx * vx + vy * vy + vz * vz);
+    if (dist <= h * simulationScale) {
+      float t = h * simulationScale - dist;
+      float h_r_2 = (float)((double)t * (double)t);
+      s1x += h_r_2 * vx / dist;
+      s1y += h_r_2 * vy / dist;
+      s1z += h_r_2 * vz / dist;
+      sum2 += h_r_2 * h_r_2;
+    }
+  }
+  double sum1 = s1x * s1x + s1y * s1y + s1z * s1z;
+  return (float)(1.0 / (beta * gradW * gradW * (sum1 + sum2)));
+}
+
+int sph_params_set_box(sph_params *p, double mx, double my, double mz) {
+  if (!p) return fail(SPH_E_INVALID, "null params");
+  double xd = mx * p->h, yd = my * p->h, zd = mz * p->h;  // `#define XMAX 30.0*h`
+  p->xmin = 0; p->ymin = 0; p->zmin = 0;
+  p->xmax = (float)xd; p->ymax = (float)yd; p->zmax = (float)zd;
+  p->grid_cells_x = (int)((xd - 0) / p->h) + 1;            // owOpenCLSolver.cpp:14-17
+  p->grid_cells_y = (int)((yd - 0) / p->h) + 1;
+  p->grid_cells_z = (int)((zd - 0) / p->h) + 1;
+  p->grid_cell_count = p->grid_cells_x * p->grid_cells_y * p->grid_cells_z;
+  return 0;
+}
+
+int sph_params_default(sph_params *p) {
+  if (!p) return fail(SPH_E_INVALID, "null params");
+  memset(p, 0, sizeof *p);
+  const float rho0 = 1000.0f, mass = 3.25e-14f, timeStep = 5.0e-06f;
+  const float simulationScale = 0.004f * powf(mass, 1.f / 3.f) / powf(0.00025f, 1.f / 3.f);
+  const float h = 3.34f;
+  p->muscle_count = 100;
+  p->max_iteration = 3;
+  p->hash_mask = 0xffffu;
+  p->h = h;
+  p->hash_grid_cell_size = 2.0f * h;
+  p->hash_grid_cell_size_inv = 1.0f / p->hash_grid_cell_size;
+  p->simulation_scale = simulationScale;
+  p->simulation_scale_inv = 1.0f / simulationScale;
+  p->r0 = 0.5f * h;
+  p->rho0 = rho0; p->mass = mass; p->time_step = timeStep;
+  p->stiffness = 0.75f; p->viscosity = 0.00005f; p->damping = 0.75f;
+  p->gravity_x = 0.0f; p->gravity_y = -9.8f; p->gravity_z = 0.0f;
+  const double beta = timeStep * timeStep * mass * mass * 2 / (rho0 * rho0);
+  p->wpoly6_coefficient = 315.0 / (64.0 * M_PI * pow((double)(h * simulationScale), 9.0));
+  p->grad_wspiky_coefficient = -45.0 / (M_PI * pow((double)(h * simulationScale), 6.0));
+  p->del2_wviscosity_coefficient = -p->grad_wspiky_coefficient;
+  p->delta = calc_delta(mass, rho0, h, simulationScale, beta, p->grad_wspiky_coefficient);
+  return sph_params_set_box(p, 30.0, 20.0, 250.0);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------- context
+static void fill_dev_params(sph_ctx *c) {
+  const sph_params &p = c->p;
+  DevParams &d = c->d;
+  d.N = p.particle_count;
+  d.Npad = ((p.particle_count + 31) / 32) * 32;
+  d.G = p.grid_cell_count;
+  d.gx = p.grid_cells_x; d.gy = p.grid_cells_y; d.gz = p.grid_cells_z;
+  d.mask = p.hash_mask;
+  d.numElastic = p.num_elastic; d.elasticOffset = p.elastic_offset; d.muscleCount = p.muscle_count;
+  d.h = p.h; d.cellSize = p.hash_grid_cell_size; d.cellSizeInv = p.hash_grid_cell_size_inv;
+  d.simScale = p.simulation_scale; d.simScaleInv = p.simulation_scale_inv; d.r0 = p.r0;
+  d.xmin = p.xmin; d.xmax = p.xmax; d.ymin = p.ymin; d.ymax = p.ymax; d.zmin = p.zmin; d.zmax = p.zmax;
+  d.rho0 = p.rho0; d.dt = p.time_step; d.delta = p.delta;
+  d.gravx = p.gravity_x; d.gravy = p.gravity_y; d.gravz = p.gravity_z;
+  d.hScaled = p.h * p.simulation_scale;
+  d.hScaled2 = d.hScaled * d.hScaled;
+  d.hScaled6 = d.hScaled2 * d.hScaled2 * d.hScaled2;
+  d.surfCoeff = (-1.5e-09f * 0.3f * (float)(p.wpoly6_coefficient * pow(d.hScaled2 / 2.0, 3.0)) * p.simulation_scale);
+  d.massMu = (float)(p.mass * p.viscosity);
+  d.posTimeStep = p.time_step * p.simulation_scale_inv;
+  d.rho0delta = p.rho0 * p.delta;
+  d.xmaxClamp = p.xmax - 0.000001f; d.ymaxClamp = p.ymax - 0.000001f; d.zmaxClamp = p.zmax - 0.000001f;
+  d.massWpoly6 = ((double)p.mass) * p.wpoly6_coefficient;
+  d.del2W = p.del2_wviscosity_coefficient;
+  d.massGradW = ((double)p.mass) * p.grad_wspiky_coefficient;
+  d.closeThr = 0.5 * (d.hScaled / 2);
+}
+
+template <class T>
+static cudaError_t dalloc(T **ptr, size_t count, bool zero = true) {
+  size_t bytes = sizeof(T) * (count ? count : 1);
+  cudaError_t e = cudaMalloc((void **)ptr, bytes);
+  if (e == cudaSuccess && zero) e = cudaMemset(*ptr, 0, bytes);
+  return e;
+}
+
+extern "C" {
+
+void sph_destroy(sph_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
+                  c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
+                  c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
+                  c->sortedType, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
+  for (void *q : ptrs)
+    if (q) cudaFree(q);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, const float *elastic4,
+                    const int32_t *membranes3, const int32_t *pml7, int device) {
+  if (!p || !pos4 || !vel4 || p->particle_count <= 0 || p->grid_cell_count <= 0 || p->grid_cells_x <= 0 ||
+      p->grid_cells_y <= 0 || p->muscle_count < 0) {
+    fail(SPH_E_INVALID, "sph_create: bad arguments");
+    return nullptr;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0) {
+    fail(SPH_E_DEVICE, std::string("sph_create: no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    return nullptr;
+  }
+  if (device < 0 || device >= ndev) {
+    fail(SPH_E_INVALID, "sph_create: bad device ordinal");
+    return nullptr;
+  }
+  if ((e = cudaSetDevice(device)) != cudaSuccess) {
+    fail(SPH_E_DEVICE, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    return nullptr;
+  }
+  sph_ctx *c = new sph_ctx();
+  memset(c, 0, sizeof *c);
+  c->p = *p;
+  c->device = device;
+  fill_dev_params(c);
+  const size_t N = c->d.N, G = c->d.G, Npad = c->d.Npad;
+  c->has_membranes = membranes3 && p->num_membranes > 0;
+  c->has_elastic = elastic4 && p->num_elastic > 0;
+  c->has_pml = c->has_membranes && c->has_elastic && pml7;
+  c->scanTiles = sph_scan_tiles_for((int)G + 1);
+  bool ok = true;
+#define A(x) ok = ok && ((e = (x)) == cudaSuccess)
+  A(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  A(dalloc(&c->position, 2 * N));
+  A(dalloc(&c->velocity, 2 * N));
+  A(dalloc(&c->particleIndex, N));
+  A(dalloc(&c->particleIndexBack, N));
+  A(dalloc(&c->sortedPosition, 2 * N));
+  A(dalloc(&c->sortedVelocity, N));
+  A(dalloc(&c->gridCellIndex, G + 1));
+  A(dalloc(&c->cellStart, G + 2));
+  A(dalloc(&c->rho, 2 * N));
+  A(dalloc(&c->pressure, N));
+  A(dalloc(&c->acceleration, 2 * N));
+  A(dalloc(&c->muscle, (size_t)p->muscle_count));
+  A(dalloc(&c->nbIds, Npad * SPH_NB));
+  A(dalloc(&c->cellCount, G + 2));
+  A(dalloc(&c->key, N));
+  A(dalloc(&c->tmpSerial, N));
+  A(dalloc(&c->sortedType, N));
+  A(dalloc(&c->scanState, (size_t)c->scanTiles));
+  A(dalloc(&c->scanTicket, 1));
+  if (ok) A(cudaMemcpy(c->position, pos4, 16 * N, cudaMemcpyHostToDevice));   // owOpenCLSolver.cpp:65
+  if (ok) A(cudaMemcpy(c->velocity, vel4, 16 * N, cudaMemcpyHostToDevice));   // :66
+  if (ok && c->has_membranes) {                                                // :70-71
+    A(dalloc(&c->membraneData, 3 * (size_t)p->num_membranes));
+    if (ok) A(cudaMemcpy(c->membraneData, membranes3, 12 * (size_t)p->num_membranes, cudaMemcpyHostToDevice));
+  }
+  if (ok && c->has_pml) {                                                      // :75-76
+    A(dalloc(&c->pml, 7 * (size_t)p->num_elastic));
+    if (ok) A(cudaMemcpy(c->pml, pml7, 28 * (size_t)p->num_elastic, cudaMemcpyHostToDevice));
+  }
+  if (ok && c->has_elastic) {                                                  // :83-86
+    A(dalloc(&c->elastic, (size_t)SPH_NB * p->num_elastic));
+    if (ok) A(cudaMemcpy(c->elastic, elastic4, 16 * (size_t)SPH_NB * p->num_elastic, cudaMemcpyHostToDevice));
+  }
+#undef A
+  if (!ok) {
+    fail(e == cudaErrorMemoryAllocation ? SPH_E_NOMEM : SPH_E_DEVICE, std::string("sph_create: ") + cudaGetErrorString(e));
+    sph_destroy(c);
+    return nullptr;
+  }
+  return c;
+}
+
+int sph_get_params(const sph_ctx *c, sph_params *out) {
+  if (!c || !out) return fail(SPH_E_INVALID, "null");
+  *out = c->p;
+  return 0;
+}
+
+static int check_launch(sph_ctx *c, bool sync) {
+  CU(cudaGetLastError());
+  if (sync) CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// ---------------------------------------------------------------- the 18 reference stages
+int sph_stage(sph_ctx *c, int stage) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  CU(cudaSetDevice(c->device));
+  switch (stage) {
+    case SPH_STAGE_CLEAR_BUFFERS: launch_clear_neighbors(c); break;
+    case SPH_STAGE_HASH_PARTICLES: launch_hash_count(c, true); break;
+    case SPH_STAGE_SORT: launch_sort(c, false); break;
+    case SPH_STAGE_SORT_POST_PASS: launch_reorder(c); break;
+    case SPH_STAGE_INDEXX: launch_indexx_compat(c); break;
+    case SPH_STAGE_INDEX_POST_PASS: break;  // gridCellIndexFixedUp IS the scan output of SORT
+    case SPH_STAGE_FIND_NEIGHBORS: launch_find_neighbors(c, false); break;
+    case SPH_STAGE_COMPUTE_DENSITY: launch_compute_density(c); break;
+    case SPH_STAGE_COMPUTE_FORCES_INIT_PRESSURE: launch_forces(c, false); break;
+    case SPH_STAGE_COMPUTE_ELASTIC_FORCES: launch_elastic(c); break;
+    case SPH_STAGE_PREDICT_POSITIONS: launch_predict_positions(c); break;
+    case SPH_STAGE_PREDICT_DENSITY: launch_predict_density(c, false); break;
+    case SPH_STAGE_CORRECT_PRESSURE: launch_correct_pressure(c); break;
+    case SPH_STAGE_COMPUTE_PRESSURE_FORCE_ACCELERATION: launch_pressure_force(c, 0); break;
+    case SPH_STAGE_INTEGRATE: launch_integrate(c); break;
+    case SPH_STAGE_CLEAR_MEMBRANE_BUFFERS: launch_clear_membrane_buffers(c); break;
+    case SPH_STAGE_MEMBRANE_INTERACTION: launch_membrane_interaction(c, false); break;
+    case SPH_STAGE_MEMBRANE_FINALIZE: launch_membrane_finalize(c); break;
+    default: return fail(SPH_E_INVALID, "unknown stage");
+  }
+  return check_launch(c, true);  // QUEUE_EACH_KERNEL 1: every stage is synchronous
+}
+
+// ---------------------------------------------------------------- fused step
+int sph_step(sph_ctx *c) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  CU(cudaSetDevice(c->device));
+  launch_hash_count(c, false);
+  launch_sort(c, true);
+  launch_find_neighbors(c, true);
+  launch_forces(c, true);
+  launch_elastic(c);
+  const int iters = c->p.max_iteration < 1 ? 1 : c->p.max_iteration;  // do{}while: at least one pass
+  for (int it = 0; it < iters; it++) {
+    launch_predict_density(c, true);
+    launch_pressure_force(c, it + 1 < iters ? 1 : 2);
+  }
+  launch_membrane_interaction(c, true);
+  return check_launch(c, false);
+}
+
+int sph_sync(sph_ctx *c) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int sph_set_muscles(sph_ctx *c, const float *signal, int n) {
+  if (!c || !signal || n < 0 || n > c->p.muscle_count) return fail(SPH_E_INVALID, "sph_set_muscles: bad arguments");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(c->muscle, signal, 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// ---------------------------------------------------------------- buffer access (reference layout)
+static void *dev_ptr(const sph_ctx *c, int id, size_t *bytes) {
+  const size_t N = c->d.N, G = c->d.G, Ne = c->has_elastic ? c->p.num_elastic : 0;
+  switch (id) {
+    case SPH_BUF_POSITION: *bytes = 2 * N * 16; return c->position;
+    case SPH_BUF_VELOCITY: *bytes = 2 * N * 16; return c->velocity;
+    case SPH_BUF_PARTICLE_INDEX: *bytes = N * 8; return c->particleIndex;
+    case SPH_BUF_PARTICLE_INDEX_BACK: *bytes = N * 4; return c->particleIndexBack;
+    case SPH_BUF_SORTED_POSITION: *bytes = 2 * N * 16; return c->sortedPosition;
+    case SPH_BUF_SORTED_VELOCITY: *bytes = N * 16; return c->sortedVelocity;
+    case SPH_BUF_GRID_CELL_INDEX: *bytes = (G + 1) * 4; return c->gridCellIndex;
+    case SPH_BUF_GRID_CELL_INDEX_FIXED_UP: *bytes = (G + 1) * 4; return c->cellStart;
+    case SPH_BUF_NEIGHBOR_MAP: *bytes = N * SPH_NB * 8; return c->nbIds;  // materialised in sph_read
+    case SPH_BUF_RHO: *bytes = 2 * N * 4; return c->rho;
+    case SPH_BUF_PRESSURE: *bytes = N * 4; return c->pressure;
+    case SPH_BUF_ACCELERATION: *bytes = 2 * N * 16; return c->acceleration;
+    case SPH_BUF_ELASTIC_CONNECTIONS: *bytes = Ne * SPH_NB * 16; return c->elastic;
+    case SPH_BUF_MEMBRANE_DATA: *bytes = c->has_membranes ? 12 * (size_t)c->p.num_membranes : 0; return c->membraneData;
+    case SPH_BUF_PARTICLE_MEMBRANES_LIST: *bytes = c->has_pml ? 28 * (size_t)c->p.num_elastic : 0; return c->pml;
+    case SPH_BUF_MUSCLE_ACTIVATION_SIGNAL: *bytes = 4 * (size_t)c->p.muscle_count; return c->muscle;
+  }
+  *bytes = 0;
+  return nullptr;
+}
+
+size_t sph_buffer_bytes(const sph_ctx *c, int id) {
+  size_t b = 0;
+  if (c) dev_ptr(c, id, &b);
+  return b;
+}
+
+int sph_read(sph_ctx *c, int id, void *dst, size_t bytes) {
+  if (!c || !dst) return fail(SPH_E_INVALID, "sph_read: null");
+  size_t have = 0;
+  void *src = dev_ptr(c, id, &have);
+  if (!src && bytes) return fail(SPH_E_UNSUPPORTED, "sph_read: buffer absent");
+  if (bytes > have) return fail(SPH_E_SIZE, "sph_read: too many bytes");
+  CU(cudaSetDevice(c->device));
+  if (id == SPH_BUF_NEIGHBOR_MAP) {
+    if (!c->nmScratch) {
+      cudaError_t e = cudaMalloc((void **)&c->nmScratch, have);
+      if (e != cudaSuccess) return fail(SPH_E_NOMEM, "sph_read: neighborMap scratch");
+    }
+    launch_materialize_neighbor_map(c, c->nmScratch);
+    CU(cudaGetLastError());
+    src = c->nmScratch;
+  }
+  if (id == SPH_BUF_GRID_CELL_INDEX) {  // indexx output is derived from the scan on demand
+    launch_indexx_compat(c);
+    CU(cudaGetLastError());
+  }
+  CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int sph_write(sph_ctx *c, int id, const void *src, size_t bytes) {
+  if (!c || !src) return fail(SPH_E_INVALID, "sph_write: null");
+  if (id != SPH_BUF_POSITION && id != SPH_BUF_VELOCITY) return fail(SPH_E_UNSUPPORTED, "sph_write: buffer not writable");
+  size_t have = 0;
+  void *dst = dev_ptr(c, id, &have);
+  if (bytes > have) return fail(SPH_E_SIZE, "sph_write: too many bytes");
+  CU(cudaSetDevice(c->device));
+  CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+}  // extern "C"

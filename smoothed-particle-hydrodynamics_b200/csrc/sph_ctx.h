@@ -1,0 +1,64 @@
+// sph_ctx.h — host-side context of libsph_b200.so and the launcher prototypes
+// implemented in the .cu files. Buffer names follow owOpenCLSolver.h:72-97.
+#pragma once
+#include "sph_device.cuh"
+
+struct sph_ctx {
+  sph_params p;
+  DevParams d;
+  int device;
+  cudaStream_t stream;
+  // ---- buffers kept in the reference layout ----
+  float4 *position;            // 2N  [0,N) x,y,z,type original order; [N,2N) membrane displacement
+  float4 *velocity;            // 2N
+  uint2 *particleIndex;        // N   (cellId, serialId), sorted after SORT
+  unsigned *particleIndexBack; // N
+  float4 *sortedPosition;      // 2N  [N,2N) predicted positions
+  float4 *sortedVelocity;      // N
+  unsigned *gridCellIndex;     // G+1 (only materialised by the INDEXX stage)
+  unsigned *cellStart;         // G+1 == gridCellIndexFixedUp (exclusive scan of the cell histogram)
+  float *rho;                  // 2N
+  float *pressure;             // N
+  float4 *acceleration;        // 2N
+  float4 *elastic;             // 32*Ne
+  int *membraneData;           // 3*M
+  int *pml;                    // 7*Ne
+  float *muscle;               // muscle_count
+  // ---- internal ----
+  int *nbIds;                  // Npad*32 int32 neighbour ids, 32x32 tiles (see nb_index)
+  unsigned *cellCount;         // G+1 (+pad) histogram, reused as scatter cursor
+  unsigned *key;               // N cell id per original particle
+  unsigned *tmpSerial;         // N counting-sort scatter target
+  float *sortedType;           // N type tag (position.w) in sorted order
+  unsigned long long *scanState;  // decoupled look-back tile states
+  unsigned *scanTicket;
+  int scanTiles;
+  unsigned epoch;              // step counter for the scan state (no per-step reset needed)
+  float2 *nmScratch;           // 32N float2, lazily allocated for sph_read(NEIGHBOR_MAP)
+  float4 *readScratch;
+  bool has_elastic, has_membranes, has_pml;
+  bool neighbors_valid;
+};
+
+// sph_sort.cu
+void launch_hash_count(sph_ctx *c, bool write_pairs);
+void launch_sort(sph_ctx *c, bool fuse_reorder);   // scan + scatter + rank (+ reorder)
+void launch_reorder(sph_ctx *c);                   // sortPostPass on the sorted particleIndex
+void launch_indexx_compat(sph_ctx *c);
+// sph_neighbors.cu
+void launch_clear_neighbors(sph_ctx *c);
+void launch_find_neighbors(sph_ctx *c, bool with_density);
+void launch_materialize_neighbor_map(sph_ctx *c, float2 *out);
+// sph_pcisph.cu
+void launch_compute_density(sph_ctx *c);
+void launch_forces(sph_ctx *c, bool fuse_predict);
+void launch_elastic(sph_ctx *c);
+void launch_predict_positions(sph_ctx *c);
+void launch_predict_density(sph_ctx *c, bool fuse_correct);
+void launch_correct_pressure(sph_ctx *c);
+void launch_pressure_force(sph_ctx *c, int mode);  // 0 = force only, 1 = + predictPositions, 2 = + integrate
+void launch_integrate(sph_ctx *c);
+// sph_membranes.cu
+void launch_clear_membrane_buffers(sph_ctx *c);
+void launch_membrane_interaction(sph_ctx *c, bool fuse_finalize);
+void launch_membrane_finalize(sph_ctx *c);

@@ -1,0 +1,60 @@
+// sph_device.cuh — shared device-side definitions of the B200 PCISPH step.
+//
+// Arithmetic contract (DESIGN.md "Numerics"): every float expression is evaluated
+// with IEEE round-to-nearest single operations in the reference's association
+// order (sphFluid.cl is built with -cl-opt-disable: no FMA contraction), so the
+// library is compiled with -fmad=false -prec-div=true -prec-sqrt=true -ftz=false
+// and results are bit-identical to the reference kernels compiled as C++.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "sph_capi.h"
+
+#define SPH_NB 32                 // MAX_NEIGHBOR_COUNT, owOpenCLConstant.h:4
+#define SPH_NO_ID (-1)            // NO_PARTICLE_ID
+#define SPH_RADIUS_SEGMENTS 30    // sphFluid.cl:116
+
+// Kernel-visible parameters: sph_params plus sub-expressions hoisted to the host
+// (computed there with the reference's exact expressions, see sph_capi.cu).
+struct DevParams {
+  int N;        // particles
+  int Npad;     // N rounded up to 32 (one neighbour tile = 32 particles)
+  int G;        // hash grid cells
+  int gx, gy, gz;
+  unsigned mask;
+  int numElastic, elasticOffset, muscleCount;
+  float h, cellSize, cellSizeInv, simScale, simScaleInv, r0;
+  float xmin, xmax, ymin, ymax, zmin, zmax;
+  float rho0, dt, delta, gravx, gravy, gravz;
+  float hScaled, hScaled2, hScaled6;  // sphFluid.cl:495-497
+  float surfCoeff;                    // sphFluid.cl:662
+  float massMu;                       // sphFluid.cl:688
+  float posTimeStep;                  // timeStep*simulationScaleInv, sphFluid.cl:928,1738
+  float rho0delta;                    // rho0*delta, sphFluid.cl:1168
+  float xmaxClamp, ymaxClamp, zmaxClamp;  // xmax-0.000001f ..., sphFluid.cl:1753-1755
+  double massWpoly6;                  // sphFluid.cl:516,1057
+  double del2W;                       // del2WviscosityCoefficient
+  double massGradW;                   // sphFluid.cl:1194
+  double closeThr;                    // 0.5*(hScaled/2), sphFluid.cl:1166
+};
+
+// ---- float4 lane-wise helpers (OpenCL vector semantics, one IEEE op per lane) ----
+__device__ __forceinline__ float4 f4(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
+__device__ __forceinline__ float4 operator+(float4 a, float4 b) { return f4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ float4 operator-(float4 a, float4 b) { return f4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
+__device__ __forceinline__ float4 operator-(float4 a) { return f4(-a.x, -a.y, -a.z, -a.w); }
+__device__ __forceinline__ float4 operator*(float4 a, float s) { return f4(a.x * s, a.y * s, a.z * s, a.w * s); }
+__device__ __forceinline__ float4 operator*(float s, float4 a) { return f4(s * a.x, s * a.y, s * a.z, s * a.w); }
+__device__ __forceinline__ float4 operator/(float4 a, float s) { return f4(a.x / s, a.y / s, a.z / s, a.w / s); }
+__device__ __forceinline__ float dot4(float4 a, float4 b) { return ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w; }
+__device__ __forceinline__ float max0(float x) { return (0.f < x) ? x : 0.f; }  // max(0.f,x), sphFluid.cl:859,1582
+
+__device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
+
+// Neighbour ids are kept as int32 in 32x32 tiles: tile t holds particles [32t, 32t+32),
+// element (k, lane) at nb[(t*32 + k)*32 + lane] — a warp reading slot k of its 32
+// particles touches one 128-byte line.
+__device__ __forceinline__ size_t nb_index(int id, int k) {
+  return ((size_t)(id >> 5) * SPH_NB + (size_t)k) * 32 + (size_t)(id & 31);
+}

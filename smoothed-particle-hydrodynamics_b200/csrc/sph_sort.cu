@@ -1,0 +1,233 @@
+// sph_sort.cu — particle-to-cell hash and a single-digit device radix (counting) sort.
+//
+// Replaces, with identical results, the reference's
+//   hashParticles        sphFluid.cl:346-383  (+ cellFactors :187-201, cellId :332-342)
+//   _runSort             owOpenCLSolver.cpp:255-261 (D2H, host qsort on the cell id, H2D)
+//   sortPostPass         sphFluid.cl:441-466
+//   indexx               sphFluid.cl:385-439   (per-cell binary search)
+//   _runIndexPostPass    owOpenCLSolver.cpp:305-319 (D2H, host backward scan, H2D)
+//
+// B200 design: the radix IS the cell id. One pass builds the cell histogram with
+// global atomics, a single-pass decoupled-look-back scan turns it into
+// gridCellIndexFixedUp directly (the closed form of indexx + the host fix-up is
+// "number of particles with a smaller cell id"), an atomic scatter bins the
+// particles, and a rank pass orders each cell by serial id — the canonical order a
+// stable sort (glibc qsort = merge sort) gives the reference — while gathering
+// position/velocity into sorted order. Nothing crosses PCIe.
+#include "sph_ctx.h"
+
+#define SCAN_THREADS 512
+#define SCAN_ITEMS 4
+#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
+
+// ---------------------------------------------------------------- hash + histogram
+template <bool WRITE_PAIRS>
+__global__ void __launch_bounds__(256) k_hash_count(DevParams d, const float4 *__restrict__ position,
+                                                    unsigned *__restrict__ key, unsigned *__restrict__ cellCount,
+                                                    uint2 *__restrict__ particleIndex) {
+  int id = blockIdx.x * blockDim.x + threadIdx.x;
+  if (id >= d.N) return;
+  float4 p = position[id];
+  // cellFactors: no xmin subtraction (sphFluid.cl:197-199); cellId (:339-340); low-bit mask (:377)
+  int cx = (int)(p.x * d.cellSizeInv);
+  int cy = (int)(p.y * d.cellSizeInv);
+  int cz = (int)(p.z * d.cellSizeInv);
+  unsigned cell = (unsigned)(cx + cy * d.gx + cz * d.gx * d.gy) & d.mask;
+  if (WRITE_PAIRS) particleIndex[id] = make_uint2(cell, (unsigned)id);
+  // The reference would index past gridCellIndex for a cell id >= G (cannot happen while
+  // integrate clamps positions into the box); keep memory safe.
+  unsigned bin = cell < (unsigned)d.G ? cell : (unsigned)d.G - 1u;
+  key[id] = cell;
+  atomicAdd(&cellCount[bin], 1u);
+}
+
+// ---------------------------------------------------------------- exclusive scan (decoupled look-back)
+// state word: [63:34] epoch, [33:32] flag (1 = aggregate, 2 = inclusive prefix), [31:0] value
+__device__ __forceinline__ unsigned long long pack_state(unsigned epoch, unsigned flag, unsigned v) {
+  return ((unsigned long long)(epoch & 0x3fffffffu) << 34) | ((unsigned long long)flag << 32) | v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_cells(unsigned *__restrict__ count, unsigned *__restrict__ start,
+                                                             int n, volatile unsigned long long *state,
+                                                             unsigned *ticket, unsigned ticketBase, unsigned epoch) {
+  __shared__ unsigned s_tile;
+  __shared__ unsigned s_warp[SCAN_THREADS / 32];
+  __shared__ unsigned s_prefix;
+  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u) - ticketBase;
+  __syncthreads();
+  const unsigned tile = s_tile;
+  const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  unsigned v[SCAN_ITEMS];
+  unsigned sum = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) {
+    v[i] = (base + i < n) ? count[base + i] : 0u;
+    sum += v[i];
+  }
+  // warp inclusive scan of per-thread sums
+  unsigned inc = sum;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned w = lane < SCAN_THREADS / 32 ? s_warp[lane] : 0u;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      unsigned t = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += t;
+    }
+    if (lane < SCAN_THREADS / 32) s_warp[lane] = w;  // inclusive warp totals
+  }
+  __syncthreads();
+  const unsigned tileTotal = s_warp[SCAN_THREADS / 32 - 1];
+  if (threadIdx.x == 0) {
+    unsigned prefix = 0;
+    if (tile == 0) {
+      state[0] = pack_state(epoch, 2u, tileTotal);
+    } else {
+      state[tile] = pack_state(epoch, 1u, tileTotal);
+      int t = (int)tile - 1;
+      while (true) {
+        unsigned long long s = state[t];
+        if ((unsigned)(s >> 34) != (epoch & 0x3fffffffu)) continue;  // not published this step yet
+        unsigned flag = (unsigned)(s >> 32) & 3u;
+        if (flag == 0u) continue;
+        prefix += (unsigned)s;
+        if (flag == 2u) break;
+        --t;
+      }
+      state[tile] = pack_state(epoch, 2u, prefix + tileTotal);
+    }
+    s_prefix = prefix;
+  }
+  __syncthreads();
+  unsigned excl = s_prefix + (warp ? s_warp[warp - 1] : 0u) + (inc - sum);
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) {
+    if (base + i < n) {
+      start[base + i] = excl;
+      count[base + i] = 0u;  // becomes the scatter cursor
+    }
+    excl += v[i];
+  }
+}
+
+// ---------------------------------------------------------------- scatter into cells (order inside a cell arbitrary)
+__global__ void __launch_bounds__(256) k_scatter(DevParams d, const unsigned *__restrict__ key,
+                                                 const unsigned *__restrict__ cellStart, unsigned *__restrict__ cursor,
+                                                 unsigned *__restrict__ tmpSerial) {
+  int id = blockIdx.x * blockDim.x + threadIdx.x;
+  if (id >= d.N) return;
+  unsigned cell = key[id];
+  unsigned bin = cell < (unsigned)d.G ? cell : (unsigned)d.G - 1u;
+  unsigned slot = cellStart[bin] + atomicAdd(&cursor[bin], 1u);
+  tmpSerial[slot] = (unsigned)id;
+}
+
+// ---------------------------------------------------------------- rank inside the cell (+ sortPostPass gather)
+// Final slot = cellStart + #(cell-mates with a smaller serial id): (cell, serial) ascending.
+template <bool REORDER>
+__global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigned *__restrict__ key,
+                                                      const unsigned *__restrict__ cellStart,
+                                                      const unsigned *__restrict__ tmpSerial,
+                                                      uint2 *__restrict__ particleIndex,
+                                                      unsigned *__restrict__ particleIndexBack,
+                                                      const float4 *__restrict__ position,
+                                                      const float4 *__restrict__ velocity,
+                                                      float4 *__restrict__ sortedPosition,
+                                                      float4 *__restrict__ sortedVelocity,
+                                                      float *__restrict__ sortedType) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= d.N) return;
+  unsigned serial = tmpSerial[s];
+  unsigned cell = key[serial];
+  unsigned bin = cell < (unsigned)d.G ? cell : (unsigned)d.G - 1u;
+  unsigned b = cellStart[bin], e = cellStart[bin + 1];
+  unsigned rank = 0;
+  for (unsigned t = b; t < e; ++t) rank += (tmpSerial[t] < serial) ? 1u : 0u;
+  unsigned dst = b + rank;
+  particleIndex[dst] = make_uint2(cell, serial);
+  if (REORDER) {  // sortPostPass, sphFluid.cl:457-465
+    float4 p = position[serial];
+    sortedType[dst] = p.w;
+    p.w = (float)(int)cell;
+    sortedVelocity[dst] = velocity[serial];
+    sortedPosition[dst] = p;
+    particleIndexBack[serial] = dst;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_reorder(DevParams d, const uint2 *__restrict__ particleIndex,
+                                                 unsigned *__restrict__ particleIndexBack,
+                                                 const float4 *__restrict__ position, const float4 *__restrict__ velocity,
+                                                 float4 *__restrict__ sortedPosition, float4 *__restrict__ sortedVelocity,
+                                                 float *__restrict__ sortedType) {
+  int id = blockIdx.x * blockDim.x + threadIdx.x;
+  if (id >= d.N) return;
+  uint2 spi = particleIndex[id];
+  float4 p = position[spi.y];
+  sortedType[id] = p.w;
+  p.w = (float)(int)spi.x;
+  sortedVelocity[id] = velocity[spi.y];
+  sortedPosition[id] = p;
+  particleIndexBack[spi.y] = (unsigned)id;
+}
+
+// indexx output for API parity (sphFluid.cl:385-439): first index per cell, -1 when empty, [0]=0, [G]=N
+__global__ void __launch_bounds__(256) k_indexx_compat(DevParams d, const unsigned *__restrict__ cellStart,
+                                                       unsigned *__restrict__ gridCellIndex) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c > d.G) return;
+  unsigned v;
+  if (c == d.G) v = (unsigned)d.N;
+  else if (c == 0) v = 0u;
+  else v = (cellStart[c + 1] > cellStart[c]) ? cellStart[c] : 0xffffffffu;
+  gridCellIndex[c] = v;
+}
+
+static inline int blocks_for(int n, int t) { return (n + t - 1) / t; }
+
+void launch_hash_count(sph_ctx *c, bool write_pairs) {
+  const int N = c->d.N;
+  cudaMemsetAsync(c->cellCount, 0, sizeof(unsigned) * ((size_t)c->d.G + 1), c->stream);
+  if (write_pairs)
+    k_hash_count<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex);
+  else
+    k_hash_count<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex);
+}
+
+void launch_sort(sph_ctx *c, bool fuse_reorder) {
+  const int N = c->d.N, n = c->d.G + 1;
+  c->epoch++;
+  unsigned ticketBase = (c->epoch - 1u) * (unsigned)c->scanTiles;
+  k_scan_cells<<<c->scanTiles, SCAN_THREADS, 0, c->stream>>>(c->cellCount, c->cellStart, n, c->scanState, c->scanTicket,
+                                                             ticketBase, c->epoch);
+  k_scatter<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->cellCount, c->tmpSerial);
+  if (fuse_reorder)
+    k_rank_reorder<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
+                                                                   c->particleIndex, c->particleIndexBack, c->position,
+                                                                   c->velocity, c->sortedPosition, c->sortedVelocity,
+                                                                   c->sortedType);
+  else
+    k_rank_reorder<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
+                                                                    c->particleIndex, c->particleIndexBack, c->position,
+                                                                    c->velocity, c->sortedPosition, c->sortedVelocity,
+                                                                    c->sortedType);
+}
+
+void launch_reorder(sph_ctx *c) {
+  k_reorder<<<blocks_for(c->d.N, 256), 256, 0, c->stream>>>(c->d, c->particleIndex, c->particleIndexBack, c->position,
+                                                            c->velocity, c->sortedPosition, c->sortedVelocity,
+                                                            c->sortedType);
+}
+
+void launch_indexx_compat(sph_ctx *c) {
+  k_indexx_compat<<<blocks_for(c->d.G + 1, 256), 256, 0, c->stream>>>(c->d, c->cellStart, c->gridCellIndex);
+}
+
+int sph_scan_tiles_for(int n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }

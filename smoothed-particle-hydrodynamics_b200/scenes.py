@@ -1,0 +1,102 @@
+"""Synthetic scenes for BASELINE configs C/D/E — host-side tooling, numpy only.
+
+A scene is the reference's own construction re-used at other sizes: liquid particles on the cubic
+r0 = h/2 lattice the reference generator uses for its outer liquid
+(/root/reference/src/owHelper.cpp:673-689: start 3*r0 from the walls, type tag 1.1, zero velocity)
+inside a one-particle-thick boundary box with inward normals stored in the velocity slot
+(/root/reference/src/owHelper.cpp:776-928: faces 1, edges 1/sqrt(2), corners 1/sqrt(3), type 3).
+A small deterministic jitter breaks the exact distance ties of a perfect lattice. The jitter comes
+from a counter-based integer hash of (seed, particle index, axis), so any sub-range of a scene can
+be generated independently (multi-GPU slabs) and does not depend on the numpy version.
+"""
+import numpy as np
+
+H = np.float32(3.34)
+R0 = np.float32(0.5) * H
+
+
+def _hash32(x):
+    """lowbias32 integer hash, vectorised on uint32."""
+    x = x.astype(np.uint32, copy=True)
+    x ^= x >> np.uint32(16)
+    x *= np.uint32(0x7FEB352D)
+    x ^= x >> np.uint32(15)
+    x *= np.uint32(0x846CA68B)
+    x ^= x >> np.uint32(16)
+    return x
+
+
+def jitter(index, axis, seed, amplitude):
+    """U(-amplitude, +amplitude) float32 for global lattice index `index` (uint64 array)."""
+    with np.errstate(over="ignore"):
+        k = (index.astype(np.uint64) * np.uint64(3) + np.uint64(axis)) & np.uint64(0xFFFFFFFF)
+        hsh = _hash32(k.astype(np.uint32) ^ _hash32(np.full(1, seed, np.uint32)))
+    u = hsh.astype(np.float64) / 4294967296.0
+    return ((2.0 * u - 1.0) * float(amplitude)).astype(np.float32)
+
+
+def liquid_block(nx, ny, nz, origin_r0=(3, 3, 3), seed=12345, jitter_frac=0.05, z_range=None, nz_total=None):
+    """nx*ny*nz liquid particles, z fastest in memory like the reference generator's loops.
+    z_range=(z0,z1) generates only lattice layers z0 <= iz < z1 of a block that is nz_total deep."""
+    z0, z1 = (0, nz) if z_range is None else z_range
+    nzt = nz if nz_total is None else nz_total
+    ix, iy, iz = np.meshgrid(np.arange(nx, dtype=np.int64), np.arange(ny, dtype=np.int64),
+                             np.arange(z0, z1, dtype=np.int64), indexing="ij")
+    ix, iy, iz = ix.ravel(), iy.ravel(), iz.ravel()
+    gidx = ((ix * ny + iy) * nzt + iz).astype(np.uint64)
+    pos = np.empty((ix.size, 4), np.float32)
+    amp = float(jitter_frac) * float(R0)
+    for a, (i, o) in enumerate(zip((ix, iy, iz), origin_r0)):
+        pos[:, a] = (i + o).astype(np.float32) * R0 + jitter(gidx, a, seed, amp)
+    pos[:, 3] = np.float32(1.1)
+    return pos, np.zeros_like(pos)
+
+
+def boundary_box(bx, by, bz):
+    """Boundary particles of a box of bx*by*bz r0-cells (box size = (bx,by,bz)*r0), all six walls."""
+    faces = []
+    for axis, n in enumerate((bx, by, bz)):
+        dims = [bx, by, bz]
+        others = [a for a in range(3) if a != axis]
+        g = np.meshgrid(*[np.arange(dims[a], dtype=np.int64) for a in others], indexing="ij")
+        for side in (0, n - 1):
+            idx = np.empty((g[0].size, 3), np.int64)
+            idx[:, axis] = side
+            idx[:, others[0]] = g[0].ravel()
+            idx[:, others[1]] = g[1].ravel()
+            faces.append(idx)
+    idx = np.unique(np.concatenate(faces), axis=0)
+    dims = np.array([bx, by, bz], np.int64)
+    f = (idx == 0).astype(np.float32) - (idx == dims - 1).astype(np.float32)
+    nn = np.abs(f).sum(1, keepdims=True)
+    nrm = f * (np.float32(1.0) / np.sqrt(nn.astype(np.float32)))
+    pos = np.empty((len(idx), 4), np.float32)
+    pos[:, :3] = (idx.astype(np.float32) + np.float32(0.5)) * R0
+    pos[:, 3] = np.float32(3.0)
+    vel = np.empty_like(pos)
+    vel[:, :3] = nrm
+    vel[:, 3] = np.float32(3.0)
+    return pos, vel
+
+
+def fluid_box(nx, ny, nz, fill_z=None, seed=12345, jitter_frac=0.05, margin=3):
+    """Liquid block nx*ny*nz (lattice counts) + boundary box leaving `margin` lattice steps to each
+    wall. fill_z: box depth in lattice steps if larger than the block (dam-break: block in the low-z
+    part). Returns (position, velocity, box multipliers in units of h)."""
+    bx, by = nx + 2 * margin, ny + 2 * margin
+    bz = (nz if fill_z is None else fill_z) + 2 * margin
+    bx, by, bz = bx + (bx & 1), by + (by & 1), bz + (bz & 1)  # box = integer multiples of h
+    lp, lv = liquid_block(nx, ny, nz, (margin, margin, margin), seed, jitter_frac)
+    bp, bv = boundary_box(bx, by, bz)
+    return np.concatenate([lp, bp]), np.concatenate([lv, bv]), (bx / 2.0, by / 2.0, bz / 2.0)
+
+
+WORKLOADS = {
+    # name: (nx, ny, nz, fill_z)  — SURVEY.md §8d
+    "dambreak_1m": (100, 100, 100, 312),      # config C: 1 M liquid, block in the low-z third
+    "fluid_8m": (200, 160, 250, None),        # config E: 8 M liquid per GPU
+    "fluid_16m": (160, 100, 1000, None),      # config D: 16 M liquid
+    "fluid_2m": (128, 128, 128, None),
+    "fluid_256k": (64, 64, 64, None),
+    "fluid_32k": (32, 32, 32, None),
+}

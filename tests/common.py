@@ -94,8 +94,14 @@ def stage_order(max_iteration=3):
 
 
 def first_mismatch(x, y):
+    """Bitwise comparison; the only tolerance: any NaN equals any NaN (x86 SSE generates the
+    negative default NaN 0xffc00000, CUDA 0x7fffffff — IEEE leaves sign/payload unspecified)."""
     bx, by = bits(x).reshape(len(x), -1), bits(y).reshape(len(y), -1)
-    d = np.argwhere(bx != by)
+    neq = bx != by
+    if np.asarray(x).dtype == np.float32 and neq.any():
+        fx, fy = np.asarray(x).reshape(len(x), -1), np.asarray(y).reshape(len(y), -1)
+        neq &= ~(np.isnan(fx) & np.isnan(fy))
+    d = np.argwhere(neq)
     if len(d) == 0:
         return None
     r = int(d[0][0])
