@@ -1,0 +1,266 @@
+#!/usr/bin/env python3
+"""bench.py — PCISPH particle-steps/s on N B200s (BASELINE.json metric), one JSON line on rank 0.
+
+  python bench.py --gpus N --steps K --warmup W [--workload NAME] [--impl reference]
+
+A step = one pass of the whole hot path (owPhysicsFluidSimulator::simulationStep's device part:
+hash/sort/neighbour search, PCISPH loop with 3 iterations, integrate, membranes) over the synthetic
+fluid named in config.workload (8 M liquid particles per GPU on the
+reference's r0 lattice in a boundary box; weak scaling).
+  value   whole-job particle-steps/s, state resident in HBM, CUDA events on the library's stream,
+          max over ranks.
+  e2e     the same metric through the reference-facing call sequence with HOST buffers: per step
+          upload the muscle signal (pinned), run the step, read position back (pinned) — what
+          simulationStep does (owPhysicsFluidSimulator.cpp:115,141).
+  roofline / cpu_baseline: see DESIGN.md "Measurement".
+--impl reference times the reference's own CPU kernels (oracle/_ref, sphFluid.cl compiled as C++;
+else the C port) with all host threads on a bounded sample of the same workload.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "smoothed-particle-hydrodynamics_b200"
+capi = importlib.import_module(PKG + ".capi")
+scenes = importlib.import_module(PKG + ".scenes")
+
+METRIC = "pcisph_particle_steps_per_s"
+UNIT = "particle-steps/s"
+B_REF = 4164  # algorithmic bytes per particle-step, SURVEY.md §8d / BASELINE.md §4
+# algorithmic bytes per particle of the reference stages each fused kernel replaces
+KERNEL_BYTES = {
+    "hash_count": 24,
+    "sort(scan+scatter+rank_reorder)": 16 + 76 + 8,
+    "find_neighbors+density": 256 + 272 + 264,
+    "forces+predict0": 356 + 92,
+    "elastic": 0,
+    "predict_density+correct_pressure": 280 + 16,
+    "pressure_force+predict": 324 + 92,
+    "pressure_force+integrate": 324 + 380,
+    "membranes": 376,
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    def __init__(self, gpu):
+        self.rows, self.proc, self.gpu = [], None, gpu
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].startswith("Active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def make_workload(name, lib):
+    nx, ny, nz, fill = scenes.WORKLOADS[name]
+    pos, vel, box = scenes.fluid_box(nx, ny, nz, fill_z=fill)
+    p = lib.default_params(box=box)
+    t = pos[:, 3].astype(np.int32)
+    p.particle_count = len(pos)
+    p.num_liquid = int((t == 1).sum())
+    p.num_boundary = int((t == 3).sum())
+    p.hash_mask = 0xFFFFFFFF  # > 65 536 cells: the reference's 16-bit mask would alias
+    return p, pos, vel
+
+
+def muscle_signal(step):
+    s = np.zeros(100, np.float32)
+    s[:96] = (0.5 + 0.5 * np.sin(0.37 * np.arange(96) + 0.9 * step)).astype(np.float32)
+    return s
+
+
+def cpu_oracle():
+    """(lib, kind, set_threads) — the reference's own kernels when oracle/_ref was built, else the C port."""
+    ref = os.path.join(ROOT, "oracle", "_ref", "libsphref.so")
+    if os.path.exists(ref):
+        L = capi.SphLib(ref)
+        return L, "reference", L.lib.sph_ref_set_threads
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import build_oracle
+    L = capi.SphLib(build_oracle.build())
+    return L, "port", L.lib.sph_oracle_set_threads
+
+
+def time_cpu(sample, steps, warmup):
+    L, kind, set_threads = cpu_oracle()
+    cores = os.cpu_count() or 1
+    set_threads(cores)
+    p, pos, vel = make_workload(sample, L)
+    ctx = L.create(p, pos, vel)
+    for _ in range(warmup):
+        ctx.step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ctx.step()
+    dt = time.perf_counter() - t0
+    n = len(pos)
+    ctx.close()
+    return {"value": n * steps / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "%s (%d particles of the same lattice fluid), %d steps after %d warm-up, %.1f s" %
+                      (sample, n, steps, warmup, dt)}, dt / steps * 1e3, n
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    steps, warmup = max(1, args.steps), max(0, min(args.warmup, 2))
+    steps = min(steps, 20)
+    cb, ms, n = time_cpu(args.cpu_sample, steps, warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "sample": args.cpu_sample, "particles_per_step": n,
+                       "pcisph_iterations": 3, "hash_mask": "0xffffffff"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="fluid_8m", choices=sorted(scenes.WORKLOADS))
+    ap.add_argument("--cpu-sample", default="fluid_256k", choices=sorted(scenes.WORKLOADS))
+    ap.add_argument("--cpu-steps", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return 0
+    warmup = max(3, args.warmup)
+    steps = max(1, args.steps)
+
+    import torch  # device enumeration, torch.distributed plumbing
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the CPU arm)")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L = capi.load_product()
+    p, pos, vel = make_workload(args.workload, L)
+    n = len(pos)
+    ctx = L.create(p, pos, vel, device=local)
+    host_pos = L.pinned_array((n, 4))
+    host_sig = L.pinned_array((100,))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        ctx.sync()
+
+    # ---- warm-up, then the device-timed region (CUDA events on the library's stream) ----
+    ctx.run_steps(warmup)
+    ctx.profile(True)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    launches0 = ctx.launch_count()
+    ms = ctx.run_steps(steps)
+    launches = ctx.launch_count() - launches0
+    clocks = sampler.stop()
+    prof = ctx.profile_report()
+    ctx.profile(False)
+    barrier()
+    # ---- e2e: host buffers in the loop, wall clock around a synchronous call sequence ----
+    e2e_steps = max(3, min(steps, 10))
+    for s in range(2):
+        ctx.set_muscles(host_sig)
+        ctx.step(sync=False)
+        ctx.read_into("position", host_pos)
+    barrier()
+    t0 = time.perf_counter()
+    for s in range(e2e_steps):
+        host_sig[:] = muscle_signal(s)
+        ctx.set_muscles(host_sig)                 # H2D 400 B (updateMuscleActivityData)
+        ctx.step(sync=False)
+        ctx.read_into("position", host_pos)       # D2H 16 N B (read_position_buffer), blocking
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    if dist is not None:
+        t = torch.tensor([ms, e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = float(t[0]), float(t[1])
+    total = n * world
+    value = total * steps / (ms * 1e-3)
+    peak, peak_src = peaks()
+    # dominant kernel of the step
+    top = max(prof, key=lambda k: prof[k]["ms"]) if prof else None
+    roof = None
+    if top:
+        avg_ms = prof[top]["ms"] / prof[top]["calls"]
+        ach = KERNEL_BYTES.get(top, 0) * n / (avg_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "avg_launch_ms": avg_ms,
+                "algorithmic_bytes_per_particle": KERNEL_BYTES.get(top, 0),
+                "step_achieved": value / world * B_REF / 1e9, "step_frac": value / world * B_REF / 1e9 / peak,
+                "kernel_share_of_step": {k: v["ms"] / (ms if ms else 1) for k, v in prof.items()}}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "particles_per_gpu": n, "liquid": int(p.num_liquid),
+                       "boundary": int(p.num_boundary), "grid_cells": int(p.grid_cell_count), "pcisph_iterations": 3,
+                       "hash_mask": "0xffffffff", "l2": "state (%.1f GB) larger than L2, no flush" % (n * 424 / 1e9),
+                       "multi_gpu": "none" if world == 1 else "independent blocks per rank (no halo exchange yet)"},
+            "clocks": clocks,
+            "e2e": {"value": total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 400,
+                    "d2h_bytes_per_step": 16 * n, "ms_per_step": e2e_ms, "steps": e2e_steps},
+            "gpu_launches": launches, "roofline": roof}
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"], _, _ = time_cpu(args.cpu_sample, args.cpu_steps, 1)
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -185,6 +185,21 @@ const char *sph_last_error(void);
 /* "cuda-sm_100a" | "oracle-c" | "reference-cl-as-c++". */
 const char *sph_backend(void);
 
+/* ---- instrumentation: no counterpart in the reference (its only timing is owHelper's
+ * stopwatch, owHelper.cpp:1806-1841); used by bench.py and the C++ facade. CUDA library only. ---- */
+
+/* Run `steps` fused steps and return the device time in ms, measured with CUDA events on the
+ * context's own stream with a synchronize on both sides. */
+int sph_run_steps(sph_ctx *ctx, int steps, float *elapsed_ms);
+/* Per-kernel CUDA-event timing of sph_step on/off; report = JSON {"kernel": {"calls":n,"ms":t}}. */
+int sph_profile_enable(sph_ctx *ctx, int on);
+int sph_profile_report(sph_ctx *ctx, char *buf, size_t n);
+/* Number of kernels sph_step has launched on this context. */
+long long sph_launch_count(const sph_ctx *ctx);
+/* Page-locked host memory for read-back / upload buffers. */
+void *sph_host_alloc(size_t bytes);
+void sph_host_free(void *p);
+
 #ifdef __cplusplus
 }
 #endif

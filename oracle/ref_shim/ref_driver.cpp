@@ -184,7 +184,7 @@ static int g_threads = 1;
 #define LAUNCH(global, call)                                            \
   do {                                                                  \
     const int _g = (global);                                            \
-    _Pragma("omp parallel for schedule(static) num_threads(g_threads)") \
+    _Pragma("omp parallel for schedule(dynamic, 512) num_threads(g_threads)") \
     for (int _i = 0; _i < _g; ++_i) {                                   \
       cl_shim_global_id = _i;                                           \
       call;                                                             \

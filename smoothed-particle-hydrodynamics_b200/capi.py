@@ -99,6 +99,17 @@ class SphLib:
         L.sph_get_params.argtypes = [C.c_void_p, P(SphParams)]
         L.sph_last_error.restype = C.c_char_p
         L.sph_backend.restype = C.c_char_p
+        self.has_instrumentation = hasattr(L, "sph_run_steps")
+        if self.has_instrumentation:  # CUDA library only
+            L.sph_run_steps.argtypes = [C.c_void_p, C.c_int, P(C.c_float)]
+            L.sph_profile_enable.argtypes = [C.c_void_p, C.c_int]
+            L.sph_profile_report.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
+            L.sph_launch_count.argtypes = [C.c_void_p]
+            L.sph_launch_count.restype = C.c_longlong
+            L.sph_host_alloc.argtypes = [C.c_size_t]
+            L.sph_host_alloc.restype = C.c_void_p
+            L.sph_host_free.argtypes = [C.c_void_p]
+            L.sph_host_free.restype = None
 
     @property
     def backend(self):
@@ -117,6 +128,15 @@ class SphLib:
         if box is not None:
             self.check(self.lib.sph_params_set_box(C.byref(p), *[float(b) for b in box]), "sph_params_set_box")
         return p
+
+    def pinned_array(self, shape, dtype=np.float32):
+        """numpy view of page-locked host memory (freed with the library; keep the lib alive)."""
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        ptr = self.lib.sph_host_alloc(n)
+        if not ptr:
+            raise SphError("sph_host_alloc failed: " + self.last_error())
+        buf = (C.c_char * n).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape)
 
     def create(self, params, position, velocity, elastic=None, membranes=None, pml=None, device=0):
         return SphContext(self, params, position, velocity, elastic, membranes, pml, device)
@@ -175,6 +195,24 @@ class SphContext:
 
     def sync(self):
         self.L.check(self.L.lib.sph_sync(self.h), "sph_sync")
+
+    def run_steps(self, steps):
+        """K fused steps timed on the device (CUDA events on the context's stream); returns ms."""
+        ms = C.c_float(0)
+        self.L.check(self.L.lib.sph_run_steps(self.h, int(steps), C.byref(ms)), "sph_run_steps")
+        return float(ms.value)
+
+    def profile(self, on):
+        self.L.check(self.L.lib.sph_profile_enable(self.h, 1 if on else 0), "sph_profile_enable")
+
+    def profile_report(self):
+        import json
+        buf = C.create_string_buffer(8192)
+        self.L.check(self.L.lib.sph_profile_report(self.h, buf, len(buf)), "sph_profile_report")
+        return json.loads(buf.value.decode())
+
+    def launch_count(self):
+        return int(self.L.lib.sph_launch_count(self.h))
 
     def set_muscles(self, signal):
         s = np.ascontiguousarray(signal, dtype=np.float32)

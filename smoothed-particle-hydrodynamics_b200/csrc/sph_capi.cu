@@ -9,6 +9,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 #include "sph_ctx.h"
 
@@ -133,6 +134,8 @@ static cudaError_t dalloc(T **ptr, size_t count, bool zero = true) {
   return e;
 }
 
+extern "C" int sph_profile_enable(sph_ctx *c, int on);
+
 extern "C" {
 
 void sph_destroy(sph_ctx *c) {
@@ -145,6 +148,7 @@ void sph_destroy(sph_ctx *c) {
                   c->sortedType, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
   for (void *q : ptrs)
     if (q) cudaFree(q);
+  if (c->profiler) sph_profile_enable(c, 0);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -266,22 +270,131 @@ int sph_stage(sph_ctx *c, int stage) {
 }
 
 // ---------------------------------------------------------------- fused step
+// Optional per-kernel timing with CUDA events on the context's own stream (bench.py roofline).
+enum { PK_HASH = 0, PK_SORT, PK_NEIGHBORS, PK_FORCES, PK_ELASTIC, PK_PREDICT_DENSITY, PK_PRESSURE_FORCE,
+       PK_PRESSURE_FORCE_INTEGRATE, PK_MEMBRANES, PK_COUNT };
+static const char *const kProfNames[PK_COUNT] = {
+    "hash_count", "sort(scan+scatter+rank_reorder)", "find_neighbors+density", "forces+predict0", "elastic",
+    "predict_density+correct_pressure", "pressure_force+predict", "pressure_force+integrate", "membranes"};
+
+struct ProfRec { int kind; cudaEvent_t a, b; };
+struct Profiler {
+  std::vector<ProfRec> recs;
+  std::vector<cudaEvent_t> pool;
+  double ms[PK_COUNT] = {0};
+  long calls[PK_COUNT] = {0};
+  cudaEvent_t get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+  }
+  void drain() {
+    for (auto &r : recs) {
+      float t = 0.f;
+      if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) { ms[r.kind] += t; calls[r.kind]++; }
+      pool.push_back(r.a); pool.push_back(r.b);
+    }
+    recs.clear();
+  }
+};
+
+struct ProfScope {
+  sph_ctx *c; Profiler *p; ProfRec r;
+  ProfScope(sph_ctx *c_, int kind) : c(c_), p((Profiler *)c_->profiler) {
+    if (p) { r.kind = kind; r.a = p->get(); r.b = p->get(); cudaEventRecord(r.a, c->stream); }
+  }
+  ~ProfScope() {
+    if (p) { cudaEventRecord(r.b, c->stream); p->recs.push_back(r); }
+  }
+};
+
 int sph_step(sph_ctx *c) {
   if (!c) return fail(SPH_E_INVALID, "null ctx");
   CU(cudaSetDevice(c->device));
-  launch_hash_count(c, false);
-  launch_sort(c, true);
-  launch_find_neighbors(c, true);
-  launch_forces(c, true);
-  launch_elastic(c);
+  { ProfScope s(c, PK_HASH); launch_hash_count(c, false); }
+  { ProfScope s(c, PK_SORT); launch_sort(c, true); }
+  { ProfScope s(c, PK_NEIGHBORS); launch_find_neighbors(c, true); }
+  { ProfScope s(c, PK_FORCES); launch_forces(c, true); }
+  if (c->d.numElastic > 0 && c->has_elastic) { ProfScope s(c, PK_ELASTIC); launch_elastic(c); }
   const int iters = c->p.max_iteration < 1 ? 1 : c->p.max_iteration;  // do{}while: at least one pass
   for (int it = 0; it < iters; it++) {
-    launch_predict_density(c, true);
-    launch_pressure_force(c, it + 1 < iters ? 1 : 2);
+    { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); }
+    const bool last = it + 1 == iters;
+    { ProfScope s(c, last ? PK_PRESSURE_FORCE_INTEGRATE : PK_PRESSURE_FORCE); launch_pressure_force(c, last ? 2 : 1); }
   }
-  launch_membrane_interaction(c, true);
+  { ProfScope s(c, PK_MEMBRANES); launch_membrane_interaction(c, true); }
+  c->launches += 7 + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
   return check_launch(c, false);
 }
+
+// ---- instrumentation (not part of the reference interface; used by bench.py / the C++ facade) ----
+int sph_profile_enable(sph_ctx *c, int on) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  Profiler *p = (Profiler *)c->profiler;
+  if (on && !p) c->profiler = new Profiler();
+  if (!on && p) {
+    cudaStreamSynchronize(c->stream);
+    p->drain();
+    for (auto e : p->pool) cudaEventDestroy(e);
+    delete p;
+    c->profiler = nullptr;
+  }
+  return 0;
+}
+
+// JSON object {"kernel name": {"calls": n, "ms": total}, ...}; resets the counters.
+int sph_profile_report(sph_ctx *c, char *buf, size_t n) {
+  if (!c || !buf || !n) return fail(SPH_E_INVALID, "sph_profile_report: null");
+  Profiler *p = (Profiler *)c->profiler;
+  if (!p) return fail(SPH_E_INVALID, "profiling is not enabled");
+  CU(cudaStreamSynchronize(c->stream));
+  p->drain();
+  std::string out = "{";
+  for (int k = 0; k < PK_COUNT; k++) {
+    if (!p->calls[k]) continue;
+    char tmp[256];
+    snprintf(tmp, sizeof tmp, "%s\"%s\": {\"calls\": %ld, \"ms\": %.6f}", out.size() > 1 ? ", " : "", kProfNames[k],
+             p->calls[k], p->ms[k]);
+    out += tmp;
+    p->calls[k] = 0; p->ms[k] = 0;
+  }
+  out += "}";
+  if (out.size() + 1 > n) return fail(SPH_E_SIZE, "sph_profile_report: buffer too small");
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return 0;
+}
+
+// K fused steps timed on the device with events on the context's stream (sync on both sides).
+int sph_run_steps(sph_ctx *c, int steps, float *elapsed_ms) {
+  if (!c || steps < 0) return fail(SPH_E_INVALID, "sph_run_steps");
+  CU(cudaSetDevice(c->device));
+  cudaEvent_t a, b;
+  CU(cudaEventCreate(&a));
+  CU(cudaEventCreate(&b));
+  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaEventRecord(a, c->stream));
+  for (int i = 0; i < steps; i++) {
+    int rc = sph_step(c);
+    if (rc) return rc;
+  }
+  CU(cudaEventRecord(b, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  float ms = 0.f;
+  CU(cudaEventElapsedTime(&ms, a, b));
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  if (elapsed_ms) *elapsed_ms = ms;
+  return 0;
+}
+
+long long sph_launch_count(const sph_ctx *c) { return c ? c->launches : 0; }
+
+// Pinned host memory for the read-back / upload buffers of the e2e path.
+void *sph_host_alloc(size_t bytes) {
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { fail(SPH_E_NOMEM, "cudaMallocHost failed"); return nullptr; }
+  return p;
+}
+void sph_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 int sph_sync(sph_ctx *c) {
   if (!c) return fail(SPH_E_INVALID, "null ctx");

@@ -38,6 +38,8 @@ struct sph_ctx {
   float4 *readScratch;
   bool has_elastic, has_membranes, has_pml;
   bool neighbors_valid;
+  void *profiler;              // Profiler* when per-kernel event timing is on
+  long long launches;          // kernels launched by sph_step so far
 };
 
 // sph_sort.cu

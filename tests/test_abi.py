@@ -12,8 +12,11 @@ from common import capi
 HEADER = os.path.join(common.ROOT, "include", "sph_capi.h")
 
 
-def declared_symbols():
+def declared_symbols(part="all"):
+    """part: 'core' = the reference-facing ABI (all three libraries), 'all' = + instrumentation (product only)."""
     text = open(HEADER).read()
+    core, _, instr = text.partition("---- instrumentation")
+    text = core if part == "core" else text
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"\b(sph_[a-z_]+)\s*\(", text)))
 
@@ -25,12 +28,13 @@ def _build_product():
 
 
 def test_header_symbols_exported_by_all_libraries():
-    syms = declared_symbols()
-    assert "sph_create" in syms and "sph_step" in syms and len(syms) >= 14
-    libs = [_build_product(), common.oracle_lib().path]
+    core, full = declared_symbols("core"), declared_symbols("all")
+    assert "sph_create" in core and "sph_step" in core and len(core) >= 14
+    assert "sph_run_steps" in full and "sph_run_steps" not in core
+    libs = [(_build_product(), full), (common.oracle_lib().path, core)]
     if common.ref_lib() is not None:
-        libs.append(common.REF_LIB)
-    for path in libs:
+        libs.append((common.REF_LIB, core))
+    for path, syms in libs:
         L = ctypes.CDLL(path)
         for s in syms:
             assert hasattr(L, s), "%s does not export %s" % (path, s)
