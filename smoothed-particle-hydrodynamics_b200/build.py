@@ -56,5 +56,34 @@ def build(force=False, verbose=False, ptxas_info=False):
     return LIB
 
 
+HOST = os.path.join(PKG, "host")
+HOST_LIB = os.path.join(PKG, "libow_b200.so")
+HOST_BIN = os.path.join(PKG, "sibernetic_b200")
+HOST_SOURCES = ["owOpenCLSolver.cpp", "owHelper.cpp", "owPhysicsFluidSimulator.cpp", "PyramidalSimulation.cpp", "ow_capi.cpp"]
+
+
+def build_host(force=False, verbose=False):
+    """The drop-in C++ classes (owPhysicsFluidSimulator / owOpenCLSolver / owHelper / PyramidalSimulation)
+    over the C-ABI -> libow_b200.so, and the headless CLI driver -> sibernetic_b200."""
+    import sysconfig
+    build()
+    srcs = [os.path.join(HOST, f) for f in HOST_SOURCES]
+    hdrs = [os.path.join(INC, "ow", f) for f in os.listdir(os.path.join(INC, "ow"))] + [os.path.join(INC, "sph_capi.h")]
+    pyinc = sysconfig.get_paths()["include"]
+    pyver = "python%d.%d" % sys.version_info[:2]
+    common = ["g++", "-std=c++17", "-O2", "-fPIC", "-Wall", "-I", INC, "-I", pyinc]
+    link = ["-L", PKG, "-lsph_b200", "-Wl,-rpath,$ORIGIN", "-l" + pyver, "-ldl", "-lm"]
+    def run(cmd):
+        if verbose:
+            print("[build]", " ".join(cmd))
+        subprocess.check_call(cmd)
+    if force or _stale(HOST_LIB, srcs + hdrs + [LIB]):
+        run(common + ["-shared"] + srcs + ["-o", HOST_LIB] + link)
+    if force or _stale(HOST_BIN, [os.path.join(HOST, "main.cpp"), HOST_LIB] + hdrs):
+        run(common + [os.path.join(HOST, "main.cpp"), "-o", HOST_BIN, "-L", PKG, "-low_b200"] + link)
+    return HOST_LIB
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True, ptxas_info="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv, verbose=True))

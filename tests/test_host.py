@@ -1,0 +1,218 @@
+"""Host-side logic of the drop-in boundary: file formats (owHelper), the Python-3 muscle hook, and —
+on a GPU — owPhysicsFluidSimulator::simulationStep through libow_b200.so against the oracle."""
+import ctypes as C
+import importlib
+import math
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import common
+
+HOSTDIR = os.path.join(common.ROOT, common.PKG, "host")
+
+
+def host_lib():
+    b = importlib.import_module(common.PKG + ".build")
+    L = C.CDLL(b.build_host())
+    L.ow_sim_create.restype = C.c_void_p
+    L.ow_sim_create.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    L.ow_sim_create_from_files.restype = C.c_void_p
+    L.ow_sim_destroy.argtypes = [C.c_void_p]
+    L.ow_sim_step.argtypes = [C.c_void_p, C.c_int]
+    L.ow_sim_step.restype = C.c_double
+    L.ow_sim_set_fused.argtypes = [C.c_void_p, C.c_int]
+    L.ow_sim_set_muscle_hook.argtypes = [C.c_void_p, C.c_int]
+    L.ow_sim_position.argtypes = [C.c_void_p]
+    L.ow_sim_position.restype = C.POINTER(C.c_float)
+    L.ow_sim_density.argtypes = [C.c_void_p]
+    L.ow_sim_density.restype = C.POINTER(C.c_float)
+    L.ow_sim_particle_index.argtypes = [C.c_void_p]
+    L.ow_sim_particle_index.restype = C.POINTER(C.c_uint)
+    L.ow_sim_read_velocity.argtypes = [C.c_void_p, C.c_void_p]
+    L.ow_muscle_signal.restype = C.POINTER(C.c_float)
+    L.ow_set_box.argtypes = [C.c_double] * 3
+    L.ow_set_configuration_files.argtypes = [C.c_char_p] * 3
+    L.ow_set_buffers_dir.argtypes = [C.c_char_p]
+    L.ow_helper_load.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.POINTER(C.c_float))] + [C.POINTER(C.c_int)] * 4
+    L.ow_helper_free_floats.argtypes = [C.POINTER(C.c_float)]
+    L.ow_helper_write_buffers.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    L.ow_helper_read_frame.argtypes = [C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.POINTER(C.c_float)),
+                                       C.POINTER(C.POINTER(C.c_int)), C.c_int]
+    L.ow_set_quiet(1)
+    return L
+
+
+def vp(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def write_txt(path, arr):
+    with open(path, "w") as f:
+        for r in arr:
+            f.write("%e\t%e\t%e\t%e\n" % tuple(float(v) for v in r))
+
+
+# ---------------------------------------------------------------- muscle hook
+def test_main_sim_known_answers():
+    sys.path.insert(0, HOSTDIR)
+    import main_sim
+    m = main_sim.muscle_simulation()
+    for t in range(3):
+        got = m.run()
+        assert len(got) == 96
+        rows = np.linspace(0, 1.5 * 2 * math.pi, 12)  # the reference's own expressions (main_sim.py:17-25)
+        w1 = [(math.sin(r - 0.0001 * t) + 1) / 2 for r in rows]
+        w2 = [(math.sin(r + math.pi - 0.0001 * t) + 1) / 2 for r in rows]
+        d1 = [x for x in w1 for _ in (0, 1)]
+        d2 = [x for x in w2 for _ in (0, 1)]
+        assert got == d1 + d2 + d2 + d1
+    # literal known answers (first call): sin(0)=0 -> 0.5; the antiphase wave mirrors it
+    m = main_sim.muscle_simulation()
+    first = m.run()
+    assert first[0] == 0.5 and first[1] == 0.5
+    assert abs(first[24] - 0.5) < 1e-15 and abs(first[2] + first[26] - 1.0) < 1e-12
+    assert abs(first[2] - (math.sin(3 * math.pi / 11) + 1) / 2) < 1e-15
+
+
+# ---------------------------------------------------------------- file formats (no GPU)
+def test_configuration_loader_and_buffers_roundtrip(tmp_path):
+    L = host_lib()
+    z = np.load(os.path.join(common.GOLDEN, "configA.npz"))
+    pos, vel = z["position"][:3000].copy(), z["velocity"][:3000].copy()
+    pos[10:20, 3] = 2.1  # a few elastic rows
+    cfg = tmp_path / "configuration"
+    cfg.mkdir()
+    write_txt(cfg / "position.txt", pos)
+    write_txt(cfg / "velocity.txt", vel)
+    con = np.full((10 * 32, 4), 0, np.float32)
+    con[:, 0] = -1
+    con[0] = (11.1, 3.3e-6, 0, 0)
+    con[32] = (10.1, 3.3e-6, 1.1, 0)
+    write_txt(cfg / "elasticconnections.txt", con)
+    with open(cfg / "position.txt", "a") as f:
+        f.write("\n")  # trailing newline-only row must not count (owHelper.cpp:1445)
+    L.ow_set_configuration_files(str(cfg).encode(), b"position.txt", b"velocity.txt")
+    n = L.ow_helper_preload()
+    assert n == 3000
+    p2, v2 = np.zeros((n, 4), np.float32), np.zeros((n, 4), np.float32)
+    cptr = C.POINTER(C.c_float)()
+    nl, ne, nb, nc = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    L.ow_helper_load(vp(p2), vp(v2), C.byref(cptr), C.byref(nl), C.byref(ne), C.byref(nb), C.byref(nc))
+    assert np.array_equal(p2, pos) and np.array_equal(v2, vel)  # %e text -> float32 round trip is exact
+    t = pos[:, 3].astype(int)
+    assert (nl.value, ne.value, nb.value) == ((t == 1).sum(), (t == 2).sum(), (t == 3).sum())
+    got = np.ctypeslib.as_array(cptr, shape=(10 * 32, 4)).copy()
+    assert np.array_equal(got, con) and nc.value == 2
+    L.ow_helper_free_floats(cptr)
+    # record (-l_to) then replay (-l_from): header = Ne, Nl; only non-boundary rows; frames appended
+    buf = tmp_path / "buffers"
+    buf.mkdir()
+    L.ow_set_buffers_dir(str(buf).encode())
+    L.ow_helper_set_counts(n, ne.value, nl.value, nb.value, 2)
+    mem = np.array([[10, 11, 12], [11, 12, 13]], np.int32)
+    L.ow_helper_write_buffers(vp(p2), vp(got), vp(mem), 1)
+    p3 = p2.copy()
+    p3[:, 0] += 1
+    L.ow_helper_write_buffers(vp(p3), None, None, 0)
+    lines = open(buf / "position_buffer.txt").read().split("\n")
+    assert int(lines[0]) == ne.value and int(lines[1]) == nl.value
+    keep = t != 3
+    assert len([x for x in lines[2:] if x]) == 2 * keep.sum()
+    pp, cc, mm = C.POINTER(C.c_float)(), C.POINTER(C.c_float)(), C.POINTER(C.c_int)()
+    frames = L.ow_helper_read_frame(C.byref(pp), C.byref(cc), C.byref(mm), 0)
+    assert frames == 2
+    f0 = np.ctypeslib.as_array(pp, shape=(int(keep.sum()), 4)).copy()
+    L.ow_helper_read_frame(C.byref(pp), C.byref(cc), C.byref(mm), 1)
+    f1 = np.ctypeslib.as_array(pp, shape=(int(keep.sum()), 4)).copy()
+    # ostream << float prints 6 significant digits (as the reference): compare at that precision
+    assert np.allclose(f0, p2[keep], rtol=2e-6) and np.allclose(f1, p3[keep], rtol=2e-6)
+    assert np.array_equal(np.ctypeslib.as_array(mm, shape=(2, 3)), mem)
+
+
+# ---------------------------------------------------------------- simulator on the GPU
+@pytest.mark.gpu
+def test_simulator_fused_and_staged_match_oracle():
+    L = host_lib()
+    O = common.oracle_lib()
+    cfg = common.config_a(O)
+    pos, vel = cfg["position"], cfg["velocity"]
+    ref = common.create(O, cfg)
+    for fused in (1, 0):
+        L.ow_set_box(36.0, 24.0, 54.0)
+        sim = L.ow_sim_create(len(pos), vp(pos), vp(vel), 0, None, 0, None, None)
+        L.ow_sim_set_fused(sim, fused)
+        L.ow_sim_set_muscle_hook(sim, 0)
+        o = common.create(O, cfg)
+        for s in range(3):
+            ms = L.ow_sim_step(sim, 0)
+            o.step()
+            assert ms > 0
+            got = np.ctypeslib.as_array(L.ow_sim_position(sim), shape=(len(pos), 4))
+            assert common.first_mismatch(got, o.read("position", len(pos))) is None
+        rho = np.ctypeslib.as_array(L.ow_sim_density(sim), shape=(len(pos),))
+        assert common.first_mismatch(rho, o.read("rho", len(pos))) is None
+        pi = np.ctypeslib.as_array(L.ow_sim_particle_index(sim), shape=(len(pos), 2))
+        assert np.array_equal(pi, o.read("particleIndex"))
+        v = np.zeros((len(pos), 4), np.float32)
+        L.ow_sim_read_velocity(sim, vp(v))
+        assert common.first_mismatch(v, o.read("velocity", len(pos))) is None
+        L.ow_sim_destroy(sim)
+    ref.close()
+
+
+@pytest.mark.gpu
+def test_simulator_worm_with_python_muscle_hook(tmp_path):
+    """Full worm config through owPhysicsFluidSimulator with the embedded-Python main_sim hook:
+    after each step the 96 signals are fetched and uploaded, as owPhysicsFluidSimulator.cpp:134-141."""
+    sys.path.insert(0, HOSTDIR)
+    import main_sim
+    L = host_lib()
+    O = common.oracle_lib()
+    cfg = common.config_worm(O)
+    pos = cfg["position"]
+    L.ow_set_box(30.0, 20.0, 250.0)
+    sim = L.ow_sim_create(len(pos), vp(pos), vp(cfg["velocity"]), int(cfg["params"].num_elastic), vp(cfg["elastic"]),
+                          len(cfg["membranes"]), vp(cfg["membranes"]), vp(cfg["pml"]))
+    o = common.create(O, cfg)
+    gen = main_sim.muscle_simulation()
+    for s in range(3):
+        L.ow_sim_step(sim, 0)
+        o.step()
+        got = np.ctypeslib.as_array(L.ow_sim_position(sim), shape=(len(pos), 4))
+        assert common.first_mismatch(got, o.read("position", len(pos))) is None, "step %d" % s
+        sig = np.zeros(100, np.float32)
+        sig[:96] = np.asarray(gen.run(), np.float32)
+        assert np.array_equal(np.ctypeslib.as_array(L.ow_muscle_signal(), shape=(100,)), sig)
+        o.set_muscles(sig)
+    L.ow_sim_destroy(sim)
+
+
+@pytest.mark.gpu
+def test_simulator_from_configuration_files_and_l_to(tmp_path):
+    L = host_lib()
+    O = common.oracle_lib()
+    cfg = common.config_a(O)
+    d = tmp_path / "configuration"
+    d.mkdir()
+    write_txt(d / "positionPureLiquid.txt", cfg["position"])
+    write_txt(d / "velocityPureLiquid.txt", cfg["velocity"])
+    (tmp_path / "buffers").mkdir()
+    L.ow_set_configuration_files(str(d).encode(), b"positionPureLiquid.txt", b"velocityPureLiquid.txt")
+    L.ow_set_buffers_dir(str(tmp_path / "buffers").encode())
+    L.ow_set_box(36.0, 24.0, 54.0)
+    sim = L.ow_sim_create_from_files()
+    L.ow_sim_set_muscle_hook(sim, 0)
+    o = common.create(O, cfg)
+    for s in range(11):
+        L.ow_sim_step(sim, 1)
+        o.step()
+    got = np.ctypeslib.as_array(L.ow_sim_position(sim), shape=(len(cfg["position"]), 4))
+    assert common.first_mismatch(got, o.read("position", len(got))) is None
+    lines = [x for x in open(tmp_path / "buffers" / "position_buffer.txt").read().split("\n") if x]
+    nl = int(cfg["params"].num_liquid)
+    assert int(lines[0]) == 0 and int(lines[1]) == nl
+    assert len(lines) - 2 == 2 * nl  # frames at step 0 and step 10 (iter_step = 10)
+    L.ow_sim_destroy(sim)
