@@ -6,6 +6,7 @@
 // runs on the CUDA device or fails with SPH_E_DEVICE.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -145,7 +146,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
+                  c->sortedType, c->spT, c->prs, c->cellList, c->cellListCount, c->cellCursor, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -184,6 +185,9 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   c->has_elastic = elastic4 && p->num_elastic > 0;
   c->has_pml = c->has_membranes && c->has_elastic && pml7;
   c->scanTiles = sph_scan_tiles_for((int)G + 1);
+  cudaDeviceGetAttribute(&c->numSMs, cudaDevAttrMultiProcessorCount, device);
+  if (c->numSMs <= 0) c->numSMs = 148;
+  { const char *e = getenv("SPH_GENERIC_NEIGHBORS"); c->force_generic_neighbors = e && e[0] == '1'; }
   bool ok = true;
 #define A(x) ok = ok && ((e = (x)) == cudaSuccess)
   A(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
@@ -204,6 +208,11 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->key, N));
   A(dalloc(&c->tmpSerial, N));
   A(dalloc(&c->sortedType, N));
+  A(dalloc(&c->spT, N));
+  A(dalloc(&c->prs, N));
+  A(dalloc(&c->cellList, (G < N ? G : N) + 1));
+  A(dalloc(&c->cellListCount, 1));
+  A(dalloc(&c->cellCursor, 1));
   A(dalloc(&c->scanState, (size_t)c->scanTiles));
   A(dalloc(&c->scanTicket, 1));
   if (ok) A(cudaMemcpy(c->position, pos4, 16 * N, cudaMemcpyHostToDevice));   // owOpenCLSolver.cpp:65

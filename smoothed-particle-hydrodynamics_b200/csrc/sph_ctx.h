@@ -30,6 +30,13 @@ struct sph_ctx {
   unsigned *key;               // N cell id per original particle
   unsigned *tmpSerial;         // N counting-sort scatter target
   float *sortedType;           // N type tag (position.w) in sorted order
+  float4 *spT;                 // N sorted (x, y, z, type tag): the copy the force kernels gather
+  float2 *prs;                 // N packed (pressure, rho*) of the fused PCISPH loop
+  unsigned *cellList;          // non-empty cells of this step (order arbitrary)
+  unsigned *cellListCount;
+  unsigned *cellCursor;        // work cursor of the tiled neighbour search
+  int numSMs;
+  bool force_generic_neighbors; // SPH_GENERIC_NEIGHBORS=1: one-thread-per-particle search (debug / A-B)
   unsigned long long *scanState;  // decoupled look-back tile states
   unsigned *scanTicket;
   int scanTiles;

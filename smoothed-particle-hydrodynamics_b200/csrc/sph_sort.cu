@@ -49,13 +49,15 @@ __device__ __forceinline__ unsigned long long pack_state(unsigned epoch, unsigne
 
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_cells(unsigned *__restrict__ count, unsigned *__restrict__ start,
                                                              int n, volatile unsigned long long *state,
-                                                             unsigned *ticket, unsigned ticketBase, unsigned epoch) {
+                                                             unsigned *ticket, unsigned ticketBase, unsigned epoch,
+                                                             unsigned *cellListCount) {
   __shared__ unsigned s_tile;
   __shared__ unsigned s_warp[SCAN_THREADS / 32];
   __shared__ unsigned s_prefix;
   if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u) - ticketBase;
   __syncthreads();
   const unsigned tile = s_tile;
+  if (tile == 0 && threadIdx.x == 0) *cellListCount = 0u;  // refilled by the rank pass below
   const int base = tile * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
   unsigned v[SCAN_ITEMS];
   unsigned sum = 0;
@@ -141,7 +143,8 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
                                                       const float4 *__restrict__ velocity,
                                                       float4 *__restrict__ sortedPosition,
                                                       float4 *__restrict__ sortedVelocity,
-                                                      float *__restrict__ sortedType) {
+                                                      float *__restrict__ sortedType, float4 *__restrict__ spT, unsigned *__restrict__ cellList,
+                                                      unsigned *__restrict__ cellListCount) {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= d.N) return;
   unsigned serial = tmpSerial[s];
@@ -151,10 +154,12 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
   unsigned rank = 0;
   for (unsigned t = b; t < e; ++t) rank += (tmpSerial[t] < serial) ? 1u : 0u;
   unsigned dst = b + rank;
+  if (rank == 0) cellList[atomicAdd(cellListCount, 1u)] = bin;  // one entry per non-empty cell
   particleIndex[dst] = make_uint2(cell, serial);
   if (REORDER) {  // sortPostPass, sphFluid.cl:457-465
     float4 p = position[serial];
     sortedType[dst] = p.w;
+    spT[dst] = p;
     p.w = (float)(int)cell;
     sortedVelocity[dst] = velocity[serial];
     sortedPosition[dst] = p;
@@ -166,12 +171,13 @@ __global__ void __launch_bounds__(256) k_reorder(DevParams d, const uint2 *__res
                                                  unsigned *__restrict__ particleIndexBack,
                                                  const float4 *__restrict__ position, const float4 *__restrict__ velocity,
                                                  float4 *__restrict__ sortedPosition, float4 *__restrict__ sortedVelocity,
-                                                 float *__restrict__ sortedType) {
+                                                 float *__restrict__ sortedType, float4 *__restrict__ spT) {
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= d.N) return;
   uint2 spi = particleIndex[id];
   float4 p = position[spi.y];
   sortedType[id] = p.w;
+  spT[id] = p;
   p.w = (float)(int)spi.x;
   sortedVelocity[id] = velocity[spi.y];
   sortedPosition[id] = p;
@@ -206,24 +212,24 @@ void launch_sort(sph_ctx *c, bool fuse_reorder) {
   c->epoch++;
   unsigned ticketBase = (c->epoch - 1u) * (unsigned)c->scanTiles;
   k_scan_cells<<<c->scanTiles, SCAN_THREADS, 0, c->stream>>>(c->cellCount, c->cellStart, n, c->scanState, c->scanTicket,
-                                                             ticketBase, c->epoch);
+                                                             ticketBase, c->epoch, c->cellListCount);
   k_scatter<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->cellCount, c->tmpSerial);
   if (fuse_reorder)
     k_rank_reorder<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                    c->particleIndex, c->particleIndexBack, c->position,
                                                                    c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                   c->sortedType);
+                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount);
   else
     k_rank_reorder<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                     c->particleIndex, c->particleIndexBack, c->position,
                                                                     c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                    c->sortedType);
+                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount);
 }
 
 void launch_reorder(sph_ctx *c) {
   k_reorder<<<blocks_for(c->d.N, 256), 256, 0, c->stream>>>(c->d, c->particleIndex, c->particleIndexBack, c->position,
                                                             c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                            c->sortedType);
+                                                            c->sortedType, c->spT);
 }
 
 void launch_indexx_compat(sph_ctx *c) {

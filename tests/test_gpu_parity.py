@@ -54,7 +54,7 @@ def D():
 
 
 def _cmp(a, b, name, tag, half=None):
-    x, y = a.read(name), b.read(name)
+    x, y = common.canon(name, a.read(name)), common.canon(name, b.read(name))
     if half == "first":
         x, y = x[: len(x) // 2], y[: len(y) // 2]
     mm = common.first_mismatch(x, y)
