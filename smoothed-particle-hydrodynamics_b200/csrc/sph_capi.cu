@@ -15,6 +15,7 @@
 #include "sph_ctx.h"
 
 int sph_scan_tiles_for(int n);
+size_t sph_neighbor_mask_words(size_t n);
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) { g_err = msg; return code; }
@@ -146,7 +147,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->prs, c->cellList, c->cellListCount, c->cellCursor, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
+                  c->sortedType, c->spT, c->prs, c->cellList, c->cellListCount, c->cellCursor, c->fnMasks, c->fnFlags, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -213,6 +214,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->cellList, (G < N ? G : N) + 1));
   A(dalloc(&c->cellListCount, 1));
   A(dalloc(&c->cellCursor, 1));
+  A(dalloc(&c->fnMasks, sph_neighbor_mask_words(N), false));
+  A(dalloc(&c->fnFlags, N));
   A(dalloc(&c->scanState, (size_t)c->scanTiles));
   A(dalloc(&c->scanTicket, 1));
   if (ok) A(cudaMemcpy(c->position, pos4, 16 * N, cudaMemcpyHostToDevice));   // owOpenCLSolver.cpp:65
@@ -331,7 +334,7 @@ int sph_step(sph_ctx *c) {
     { ProfScope s(c, last ? PK_PRESSURE_FORCE_INTEGRATE : PK_PRESSURE_FORCE); launch_pressure_force(c, last ? 2 : 1); }
   }
   { ProfScope s(c, PK_MEMBRANES); launch_membrane_interaction(c, true); }
-  c->launches += 7 + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
+  c->launches += 8 + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
   return check_launch(c, false);
 }
 

@@ -129,57 +129,56 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 }
 
 // ---------------------------------------------------------------- tiled path (the product path)
-// One CTA per non-empty hash cell ("home cell"). All particles of a cell that sit in the same
-// octant of it visit the same 8 cells in the same order, so the home particles are grouped by
-// octant and every 32-candidate chunk of those cells is tested against the whole group at once:
-// lanes hold candidates (one coalesced float4 load per chunk), home positions are broadcast from
-// shared memory two at a time and the distance test runs on Blackwell's packed fp32x2 pipe
-// (add.rn.f32x2 / mul.rn.f32x2: per-lane IEEE results, identical to the scalar reference order
-// d.x*d.x + d.y*d.y + d.z*d.z). Each (home particle, chunk) ballot is kept as a 32-bit hit mask
-// in shared memory — hits within the largest radius the reference can choose, r = 31h/30.
-// A second phase (one thread per home particle) walks its masks in the reference's scan order,
-// re-derives the exact distance of the ~35 hits, builds the 30-bin radial histogram, picks r_thr
-// (sphFluid.cl:310-324) and keeps the first 32 hits within it — the two passes of the reference
-// collapse into one sweep over the candidates. rho(t) is accumulated on the selected neighbours.
-#define FN_THREADS 64
+// Two kernels.
+//
+// P1  k_neighbor_masks — one CTA per non-empty hash cell ("home cell"). All particles of a cell that
+//     sit in the same octant of it visit the same 8 cells in the same order (sphFluid.cl:248-308), so
+//     the home particles are grouped by octant and the group's candidates are the concatenation of
+//     those 8 cells ("virtual candidate list", 32-candidate chunks). A warp takes one PAIR of home
+//     particles, keeps the pair's coordinates in registers as fp32x2 operands and sweeps the chunks:
+//     lanes hold candidates (one float4 load each), the squared distances of both home particles come
+//     out of Blackwell's packed fp32x2 pipe (add/mul/fma.rn.f32x2), two ballots give the 32-bit hit
+//     masks of the chunk, lane c keeps chunk c's masks, and at the end the warp writes each particle's
+//     mask row with one coalesced store. The test is a conservative FILTER (radius 31h/30 — the largest
+//     r_thr the reference can choose — slightly inflated, FMA allowed): nothing inexact reaches the output.
+// P2  k_neighbor_select — one thread per particle walks its mask row in the reference's scan order,
+//     re-derives the exact distance of the ~35 hits with the reference's operation order, builds the
+//     30-bin radial histogram, picks r_thr (sphFluid.cl:310-324), keeps the first 32 hits within it
+//     (:166-174) and accumulates rho(t) (pcisph_computeDensity, :472-518) on them. The two scan passes
+//     of the reference become one sweep over the candidates plus two passes over the hits.
+// Particles whose neighbourhood does not fit the tables (more than FN_LMAX candidates or FN_CAP hits)
+// take find_neighbors_one, the generic two-pass scan.
+#define FN_THREADS 128
 #define FN_WARPS (FN_THREADS / 32)
 #define FN_HB 64                 // home particles per batch
-#define FN_MAXSLOTS 48           // 32-candidate chunks per octant group (8 cells)
 #define FN_ROWS (FN_HB + 8)      // rows = home particles in group order, groups padded to even size
-#define FN_CAP 54                // hits kept per home particle (within 31h/30); more -> generic path
-#define FN_PAIRS 4               // home-particle pairs held in registers per sweep over the chunks
+#define FN_LMAX 768              // candidates per octant group (8 cells) held in the index table
+#define FN_ROWW 32               // mask words per particle row (128 B); FN_LMAX / 32 <= FN_ROWW
+#define FN_CAP 52                // hits kept per particle in P2
 
 struct FnShared {
-  float2 px[FN_ROWS / 2 + FN_PAIRS], py[FN_ROWS / 2 + FN_PAIRS], pz[FN_ROWS / 2 + FN_PAIRS];
-  union {
-    unsigned mask[FN_MAXSLOTS][FN_ROWS];  // phase 1: hit bits [slot][row]
-    float d2[FN_CAP][FN_HB];              // phase 2: exact squared distance of each kept hit
-  } u;
-  int hits[FN_CAP][FN_HB];                // phase 2: candidate ids in scan order; compacted in place to the result
-  int slotBase[8][FN_MAXSLOTS];
-  int slotCnt[8][FN_MAXSLOTS];
-  unsigned char hist[SPH_RADIUS_SEGMENTS + 2][FN_HB];
+  float2 px[FN_ROWS / 2], py[FN_ROWS / 2], pz[FN_ROWS / 2];
+  int rowId[FN_ROWS];
+  int cidx[8][FN_LMAX];
   int cellB[27], cellN[27];
-  int nslots[8], grpStart[9], grpCount[8];
-  int fallback, nextCell;
+  int cum[8][9], cbase[8][8];
+  int grpStart[9], grpCount[8], pairStart[9], bad[8];
+  int nextCell;
 };
-static_assert(sizeof(float) * FN_CAP * FN_HB <= sizeof(unsigned) * FN_MAXSLOTS * FN_ROWS, "d2 must fit in the mask area");
 
-template <bool WITH_DENSITY>
-__global__ void __launch_bounds__(FN_THREADS) k_find_neighbors_tiled(DevParams d, const float4 *__restrict__ sp,
-                                                                     const unsigned *__restrict__ cellStart,
-                                                                     const unsigned *__restrict__ cellList,
-                                                                     const unsigned *__restrict__ cellListCount,
-                                                                     unsigned *__restrict__ cellCursor,
-                                                                     int *__restrict__ nb, float *__restrict__ rho) {
+template <int DUMMY>
+__global__ void __launch_bounds__(FN_THREADS) k_neighbor_masks(DevParams d, const float4 *__restrict__ sp,
+                                                               const unsigned *__restrict__ cellStart,
+                                                               const unsigned *__restrict__ cellList,
+                                                               const unsigned *__restrict__ cellListCount,
+                                                               unsigned *__restrict__ cellCursor,
+                                                               unsigned *__restrict__ masks,
+                                                               unsigned char *__restrict__ flags) {
   __shared__ FnShared S;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nCells = (int)*cellListCount;
-  const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr, j == 30
-  // Phase 1 is only a conservative filter (phase 2 re-derives every distance exactly), so it may use
-  // FMA and a slightly inflated radius; nothing inexact reaches the output.
+  const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr (j == 30)
   const float rfilt2 = rmaxf * rmaxf * 1.0001f;
-  const float h2 = d.h * d.h;
   const float FAR = 1.0e30f;
   while (true) {
     __syncthreads();
@@ -201,7 +200,8 @@ __global__ void __launch_bounds__(FN_THREADS) k_find_neighbors_tiled(DevParams d
       const int id = b0 + tid;
       __syncthreads();
       if (tid < 8) S.grpCount[tid] = 0;
-      if (tid == 0) S.fallback = 0;
+      if (tid < FN_ROWS) S.rowId[tid] = -1;
+      if (tid < FN_ROWS / 2) { S.px[tid] = make_float2(FAR, FAR); S.py[tid] = make_float2(FAR, FAR); S.pz[tid] = make_float2(FAR, FAR); }
       __syncthreads();
       // ---- group the home particles by octant (which half of the 2h cell, per axis: :253-271)
       float4 pos = f4(0.f, 0.f, 0.f, 0.f);
@@ -215,152 +215,195 @@ __global__ void __launch_bounds__(FN_THREADS) k_find_neighbors_tiled(DevParams d
             ((((pos.z - d.zmin) - cfz) < d.h) ? 0 : 4);
         rankInG = atomicAdd(&S.grpCount[g], 1);
       }
-      for (int r = tid; r < FN_ROWS / 2 + FN_PAIRS; r += FN_THREADS) {  // unused rows: far-away dummies
-        S.px[r] = make_float2(FAR, FAR); S.py[r] = make_float2(FAR, FAR); S.pz[r] = make_float2(FAR, FAR);
-      }
       __syncthreads();
-      if (tid < 8) {  // slot table of group `tid`: its 8 cells in the reference's visiting order (:248-308)
-        int gs = 0;
-        for (int q = 0; q < tid; q++) gs += (S.grpCount[q] + 1) & ~1;
+      if (tid < 8) {  // tables of group `tid`: its 8 cells in the reference's visiting order (:248-308)
+        int gs = 0, ps = 0;
+        for (int q = 0; q < tid; q++) { gs += (S.grpCount[q] + 1) & ~1; ps += (S.grpCount[q] + 1) >> 1; }
         S.grpStart[tid] = gs;
-        int ns = 0;
-        if (S.grpCount[tid] > 0) {
-          const int sx = (tid & 1) ? 1 : -1, sy = (tid & 2) ? 1 : -1, sz = (tid & 4) ? 1 : -1;
+        S.pairStart[tid] = ps;
+        if (tid == 7) S.pairStart[8] = ps + ((S.grpCount[7] + 1) >> 1);
+        const int sx = (tid & 1) ? 1 : -1, sy = (tid & 2) ? 1 : -1, sz = (tid & 4) ? 1 : -1;
+        int L = 0;
 #pragma unroll
-          for (int k = 0; k < 8; k++) {
-            const int kx = (0xB2 >> k) & 1, ky = (0xD4 >> k) & 1, kz = (0xE8 >> k) & 1;  // own,x,y,z,xy,xz,yz,xyz
-            const int i27 = (kx * sx + 1) + (ky * sy + 1) * 3 + (kz * sz + 1) * 9;
-            const int base = S.cellB[i27], n = S.cellN[i27];
-            for (int j = 0; j < n; j += 32) {
-              if (ns < FN_MAXSLOTS) { S.slotBase[tid][ns] = base + j; S.slotCnt[tid][ns] = min(32, n - j); }
-              ns++;
-            }
-          }
-          if (ns > FN_MAXSLOTS) S.fallback = 1;
+        for (int k = 0; k < 8; k++) {
+          const int kx = (0xB2 >> k) & 1, ky = (0xD4 >> k) & 1, kz = (0xE8 >> k) & 1;  // own,x,y,z,xy,xz,yz,xyz
+          const int i27 = (kx * sx + 1) + (ky * sy + 1) * 3 + (kz * sz + 1) * 9;
+          S.cum[tid][k] = L;
+          S.cbase[tid][k] = S.cellB[i27];
+          L += S.cellN[i27];
         }
-        S.nslots[tid] = ns;
+        S.cum[tid][8] = L;
+        S.bad[tid] = (L > FN_LMAX) ? 1 : 0;
       }
       __syncthreads();
-      if (S.fallback) {  // a crowded neighbourhood: the generic two-pass scan for this batch
-        if (tid < hb) find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho);
-        continue;
+      if (tid < hb) {
+        const int row = S.grpStart[g] + rankInG;
+        ((float *)S.px)[row] = pos.x; ((float *)S.py)[row] = pos.y; ((float *)S.pz)[row] = pos.z;
+        S.rowId[row] = id;
+        flags[id] = (unsigned char)S.bad[g];
       }
-      const int row = S.grpStart[g] + rankInG;
-      if (tid < hb) { ((float *)S.px)[row] = pos.x; ((float *)S.py)[row] = pos.y; ((float *)S.pz)[row] = pos.z; }
-      __syncthreads();
-      // ---- phase 1: hit masks. Home pairs live in registers; lanes hold candidates.
+      // ---- virtual candidate list -> sorted index, per group
 #pragma unroll 1
       for (int gg = 0; gg < 8; gg++) {
-        const int cnt = S.grpCount[gg];
-        if (!cnt) continue;
-        const int pairs = (cnt + 1) >> 1, rowBase = S.grpStart[gg], ns = S.nslots[gg];
-#pragma unroll 1
-        for (int q0 = 0; q0 < pairs; q0 += FN_PAIRS) {
-          float2 hx[FN_PAIRS], hy[FN_PAIRS], hz[FN_PAIRS];
+        if (!S.grpCount[gg] || S.bad[gg]) continue;
+        const int L = S.cum[gg][8];
+        for (int v = tid; v < L; v += FN_THREADS) {
+          int k = 0;
 #pragma unroll
-          for (int q = 0; q < FN_PAIRS; q++) {
-            const int pr = (rowBase >> 1) + q0 + q;
-            hx[q] = S.px[pr]; hy[q] = S.py[pr]; hz[q] = S.pz[pr];
-          }
-#pragma unroll 1
-          for (int s = warp; s < ns; s += FN_WARPS) {
-            const int n = S.slotCnt[gg][s];
-            float4 c = f4(FAR, FAR, FAR, 0.f);
-            if (lane < n) c = ldg4(sp + S.slotBase[gg][s] + lane);
-            const float2 ncx = make_float2(-c.x, -c.x), ncy = make_float2(-c.y, -c.y), ncz = make_float2(-c.z, -c.z);
-            unsigned m[2 * FN_PAIRS];
-#pragma unroll
-            for (int q = 0; q < FN_PAIRS; q++) {
-              float2 ex = __fadd2_rn(hx[q], ncx), ey = __fadd2_rn(hy[q], ncy), ez = __fadd2_rn(hz[q], ncz);
-              float2 dd = __ffma2_rn(ez, ez, __ffma2_rn(ey, ey, __fmul2_rn(ex, ex)));
-              m[2 * q] = __ballot_sync(0xffffffffu, dd.x <= rfilt2);
-              m[2 * q + 1] = __ballot_sync(0xffffffffu, dd.y <= rfilt2);
-            }
-            if (lane == 0) {
-              unsigned *dst = &S.u.mask[s][rowBase + 2 * q0];
-#pragma unroll
-              for (int q = 0; q < FN_PAIRS; q++)
-                if (q0 + q < pairs) *reinterpret_cast<uint2 *>(dst + 2 * q) = make_uint2(m[2 * q], m[2 * q + 1]);
-            }
-          }
+          for (int q = 1; q < 8; q++) k += (v >= S.cum[gg][q]) ? 1 : 0;
+          S.cidx[gg][v] = S.cbase[gg][k] + v - S.cum[gg][k];
         }
       }
       __syncthreads();
-      // ---- phase 2a: hit masks -> per-particle candidate list in the reference's scan order
-      int nh = 0;
-      if (tid < hb) {
-        const int ns = S.nslots[g];
-        for (int s = 0; s < ns; s++) {
-          unsigned m = S.u.mask[s][row];
-          const int base = S.slotBase[g][s];
-          while (m) {
-            const int cidx = base + __ffs(m) - 1;
-            m &= m - 1;
-            if (cidx != id) {
-              if (nh < FN_CAP) S.hits[nh][tid] = cidx;
-              nh++;
-            }
-          }
-        }
+      // ---- one warp per home pair: sweep the chunks
+      const int totalPairs = S.pairStart[8];
+#pragma unroll 1
+      for (int t = warp; t < totalPairs; t += FN_WARPS) {
+        int gg = 0;
 #pragma unroll
-        for (int b = 0; b < SPH_RADIUS_SEGMENTS; b++) S.hist[b][tid] = 0;
-      }
-      __syncthreads();  // masks are dead from here on: their storage becomes d2[][]
-      if (tid < hb) {
-        if (nh > FN_CAP) {  // more hits than the list holds: generic path for this particle
-          find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho);
-        } else {
-          // ---- phase 2b: exact distances + 30-bin radial histogram of everything within h (:157-161)
-          float4 q = (nh > 0) ? ldg4(sp + S.hits[0][tid]) : pos;
-          for (int t = 0; t < nh; t++) {
-            const float4 cur = q;
-            if (t + 1 < nh) q = ldg4(sp + S.hits[t + 1][tid]);
-            float ex = pos.x - cur.x, ey = pos.y - cur.y, ez = pos.z - cur.z;
-            float dd = ex * ex + ey * ey + ez * ez;
-            S.u.d2[t][tid] = dd;
-            if (dd <= h2) {
-              int b = (int)(sqrtf(dd) * SPH_RADIUS_SEGMENTS / d.h);
-              if (b < SPH_RADIUS_SEGMENTS) {
-                unsigned v = S.hist[b][tid];
-                if (v < 255u) S.hist[b][tid] = (unsigned char)(v + 1u);  // saturation keeps the >32 logic exact
-              }
-            }
-          }
-          // ---- radius threshold (:310-324)
-          int j = 0, sum = 0;
-          while (j < SPH_RADIUS_SEGMENTS) {
-            sum += S.hist[j][tid];
-            if (sum == SPH_NB) break;
-            if (sum > SPH_NB) { j--; break; }
-            j++;
-          }
-          const float r_thr = (float)(j + 1) * d.h / SPH_RADIUS_SEGMENTS;
-          const float r2 = r_thr * r_thr;
-          // ---- phase 2c: first 32 hits within r_thr, in scan order (:166-174) + rho(t)
-          int found = 0;
-          double density = 0.0;
-          for (int t = 0; t < nh; t++) {
-            const float dd = S.u.d2[t][tid];
-            if (dd <= r2) {
-              S.hits[found][tid] = S.hits[t][tid];
-              if (WITH_DENSITY) {
-                float r = sqrtf(dd) * d.simScale;
-                float rr = r * r;
-                density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
-              }
-              if (++found == SPH_NB) break;
-            }
-          }
-#pragma unroll 8
-          for (int k = 0; k < SPH_NB; k++) nb[nb_index(id, k)] = (k < found) ? S.hits[k][tid] : SPH_NO_ID;
-          if (WITH_DENSITY) {
-            if (density < (double)d.hScaled6) density = (double)d.hScaled6;
-            density *= d.massWpoly6;
-            rho[id] = (float)density;
-          }
+        for (int q = 1; q < 8; q++) gg += (t >= S.pairStart[q]) ? 1 : 0;
+        if (S.bad[gg]) continue;
+        const int pr = (S.grpStart[gg] >> 1) + (t - S.pairStart[gg]);
+        const float2 hx = S.px[pr], hy = S.py[pr], hz = S.pz[pr];
+        const int L = S.cum[gg][8];
+        const int nch = (L + 31) >> 5;
+        unsigned keep0 = 0, keep1 = 0;
+#pragma unroll 2
+        for (int c = 0; c < nch; c++) {
+          const int v = (c << 5) + lane;
+          float4 cd = f4(FAR, FAR, FAR, 0.f);
+          if (v < L) cd = ldg4(sp + S.cidx[gg][v]);
+          const float2 ncx = make_float2(-cd.x, -cd.x), ncy = make_float2(-cd.y, -cd.y), ncz = make_float2(-cd.z, -cd.z);
+          float2 ex = __fadd2_rn(hx, ncx), ey = __fadd2_rn(hy, ncy), ez = __fadd2_rn(hz, ncz);
+          float2 dd = __ffma2_rn(ez, ez, __ffma2_rn(ey, ey, __fmul2_rn(ex, ex)));
+          const unsigned m0 = __ballot_sync(0xffffffffu, dd.x <= rfilt2);
+          const unsigned m1 = __ballot_sync(0xffffffffu, dd.y <= rfilt2);
+          if (lane == c) { keep0 = m0; keep1 = m1; }
+        }
+        const int id0 = S.rowId[2 * pr], id1 = S.rowId[2 * pr + 1];
+        if (lane < nch) {
+          masks[(size_t)id0 * FN_ROWW + lane] = keep0;
+          if (id1 >= 0) masks[(size_t)id1 * FN_ROWW + lane] = keep1;
         }
       }
     }
+  }
+}
+
+struct FnSelShared {
+  int hits[FN_CAP][FN_THREADS];
+  int cumS[9][FN_THREADS];
+  int adjS[8][FN_THREADS];
+  unsigned char hist[SPH_RADIUS_SEGMENTS + 2][FN_THREADS];
+};
+
+template <bool WITH_DENSITY>
+__global__ void __launch_bounds__(FN_THREADS) k_neighbor_select(DevParams d, const float4 *__restrict__ sp,
+                                                                const unsigned *__restrict__ cellStart,
+                                                                const unsigned *__restrict__ masks,
+                                                                const unsigned char *__restrict__ flags,
+                                                                int *__restrict__ nb, float *__restrict__ rho) {
+  __shared__ FnSelShared S;
+  const int tid = threadIdx.x;
+  const int id = blockIdx.x * FN_THREADS + tid;
+  if (id >= d.N) return;
+  if (flags[id]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); return; }
+  const float4 pos = sp[id];
+  const float h2 = d.h * d.h;
+  {  // the 8 cells of this particle and the prefix of their sizes (virtual candidate index space)
+    int cells[8];
+    neighbor_cells(d, pos, (int)pos.w & d.mask, cells);
+    int L = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      const int b = (int)cellStart[cells[k]], n = (int)cellStart[cells[k] + 1] - b;
+      S.cumS[k][tid] = L;
+      S.adjS[k][tid] = b - L;
+      L += n;
+    }
+    S.cumS[8][tid] = L;
+  }
+  const int L = S.cumS[8][tid];
+  const int nch = (L + 31) >> 5;
+  // ---- mask row -> candidate list in scan order (each thread walks words and bits at its own pace)
+  const unsigned *row = masks + (size_t)id * FN_ROWW;
+  int nh = 0;
+  {
+    int c = 0, k = 0, kend = S.cumS[1][tid], adj = S.adjS[0][tid];
+    unsigned m = nch > 0 ? __ldg(row) : 0u;
+    while (true) {
+      if (m == 0u) {
+        if (++c >= nch) break;
+        m = __ldg(row + c);
+        continue;
+      }
+      const int v = (c << 5) + __ffs(m) - 1;
+      m &= m - 1;
+      while (v >= kend) { ++k; kend = S.cumS[k + 1][tid]; adj = S.adjS[k][tid]; }
+      const int cidx = v + adj;
+      if (cidx != id) {
+        if (nh < FN_CAP) S.hits[nh][tid] = cidx;
+        nh++;
+      }
+    }
+  }
+  if (nh > FN_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); return; }
+#pragma unroll
+  for (int b = 0; b < SPH_RADIUS_SEGMENTS; b++) S.hist[b][tid] = 0;
+  // ---- exact distances + 30-bin radial histogram of everything within h (:157-161)
+  {
+    float4 q = (nh > 0) ? ldg4(sp + S.hits[0][tid]) : pos;
+    for (int t = 0; t < nh; t++) {
+      const float4 cur = q;
+      if (t + 1 < nh) q = ldg4(sp + S.hits[t + 1][tid]);
+      float ex = pos.x - cur.x, ey = pos.y - cur.y, ez = pos.z - cur.z;
+      float dd = ex * ex + ey * ey + ez * ez;
+      if (dd <= h2) {
+        int b = (int)(sqrtf(dd) * SPH_RADIUS_SEGMENTS / d.h);
+        if (b < SPH_RADIUS_SEGMENTS) {
+          unsigned v = S.hist[b][tid];
+          if (v < 255u) S.hist[b][tid] = (unsigned char)(v + 1u);  // saturation keeps the >32 logic exact
+        }
+      }
+    }
+  }
+  // ---- radius threshold (:310-324)
+  int j = 0, sum = 0;
+  while (j < SPH_RADIUS_SEGMENTS) {
+    sum += S.hist[j][tid];
+    if (sum == SPH_NB) break;
+    if (sum > SPH_NB) { j--; break; }
+    j++;
+  }
+  const float r_thr = (float)(j + 1) * d.h / SPH_RADIUS_SEGMENTS;
+  const float r2 = r_thr * r_thr;
+  // ---- first 32 hits within r_thr, in scan order (:166-174) + rho(t)
+  int found = 0;
+  double density = 0.0;
+  {
+    float4 q = (nh > 0) ? ldg4(sp + S.hits[0][tid]) : pos;
+    for (int t = 0; t < nh; t++) {
+      const float4 cur = q;
+      if (t + 1 < nh) q = ldg4(sp + S.hits[t + 1][tid]);
+      float ex = pos.x - cur.x, ey = pos.y - cur.y, ez = pos.z - cur.z;
+      float dd = ex * ex + ey * ey + ez * ez;
+      if (dd <= r2) {
+        S.hits[found][tid] = S.hits[t][tid];
+        if (WITH_DENSITY) {
+          float r = sqrtf(dd) * d.simScale;
+          float rr = r * r;
+          density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
+        }
+        if (++found == SPH_NB) break;
+      }
+    }
+  }
+#pragma unroll 8
+  for (int k = 0; k < SPH_NB; k++) nb[nb_index(id, k)] = (k < found) ? S.hits[k][tid] : SPH_NO_ID;
+  if (WITH_DENSITY) {
+    if (density < (double)d.hScaled6) density = (double)d.hScaled6;
+    density *= d.massWpoly6;
+    rho[id] = (float)density;
   }
 }
 
@@ -395,21 +438,26 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
       k_find_neighbors_generic<false><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho);
     return;
   }
-  // persistent CTAs (one resident wave), cells handed out through an atomic cursor
+  // P1: persistent CTAs (one resident wave), cells handed out through an atomic cursor; P2: one thread per particle
   static int occ = 0;
   if (!occ) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_find_neighbors_tiled<true>, FN_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_neighbor_masks<0>, FN_THREADS, 0);
     if (occ < 1) occ = 1;
   }
-  const int grid = c->numSMs * occ;
   cudaMemsetAsync(c->cellCursor, 0, sizeof(unsigned), c->stream);
+  k_neighbor_masks<0><<<c->numSMs * occ, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->cellList,
+                                                                   c->cellListCount, c->cellCursor, c->fnMasks,
+                                                                   c->fnFlags);
+  const int blocks = (c->d.N + FN_THREADS - 1) / FN_THREADS;
   if (with_density)
-    k_find_neighbors_tiled<true><<<grid, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->cellList,
-                                                                   c->cellListCount, c->cellCursor, c->nbIds, c->rho);
+    k_neighbor_select<true><<<blocks, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->fnMasks,
+                                                                 c->fnFlags, c->nbIds, c->rho);
   else
-    k_find_neighbors_tiled<false><<<grid, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->cellList,
-                                                                    c->cellListCount, c->cellCursor, c->nbIds, c->rho);
+    k_neighbor_select<false><<<blocks, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->fnMasks,
+                                                                  c->fnFlags, c->nbIds, c->rho);
 }
+
+size_t sph_neighbor_mask_words(size_t n) { return n * FN_ROWW; }
 
 void launch_materialize_neighbor_map(sph_ctx *c, float2 *out) {
   size_t n = (size_t)c->d.N * SPH_NB;
