@@ -15,7 +15,6 @@
 #include "sph_ctx.h"
 
 int sph_scan_tiles_for(int n);
-size_t sph_neighbor_mask_words(size_t n);
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) { g_err = msg; return code; }
@@ -126,6 +125,21 @@ static void fill_dev_params(sph_ctx *c) {
   d.del2W = p.del2_wviscosity_coefficient;
   d.massGradW = ((double)p.mass) * p.grad_wspiky_coefficient;
   d.closeThr = 0.5 * (d.hScaled / 2);
+  // radial-histogram bin thresholds (see DevParams::binT). The bin is a monotone step function of d2.
+  auto bin_of = [&](float d2) -> int { return (int)(sqrtf(d2) * SPH_RADIUS_SEGMENTS / d.h); };
+  d.binT[0] = 0.f;
+  for (int j = 1; j <= SPH_RADIUS_SEGMENTS; j++) {
+    uint32_t lo = 0u, hi;  // bit patterns of +0 and (2h)^2: bin_of(lo) = 0 < j <= 30 < bin_of(hi) = 60
+    { float top = 4.f * d.h * d.h; memcpy(&hi, &top, 4); }
+    while (hi - lo > 1u) {
+      uint32_t mid = lo + (hi - lo) / 2u;
+      float f; memcpy(&f, &mid, 4);
+      if (bin_of(f) >= j) hi = mid; else lo = mid;
+    }
+    memcpy(&d.binT[j], &hi, 4);
+  }
+  { uint32_t inf = 0x7f800000u; memcpy(&d.binT[SPH_RADIUS_SEGMENTS + 1], &inf, 4); }
+  d.binScale = (float)SPH_RADIUS_SEGMENTS / d.h;
 }
 
 template <class T>
@@ -147,7 +161,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->prs, c->cellList, c->cellListCount, c->cellCursor, c->fnMasks, c->fnFlags, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
+                  c->sortedType, c->spT, c->prs, c->cellList, c->cellListCount, c->cellCursor, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -214,8 +228,6 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->cellList, (G < N ? G : N) + 1));
   A(dalloc(&c->cellListCount, 1));
   A(dalloc(&c->cellCursor, 1));
-  A(dalloc(&c->fnMasks, sph_neighbor_mask_words(N), false));
-  A(dalloc(&c->fnFlags, N));
   A(dalloc(&c->scanState, (size_t)c->scanTiles));
   A(dalloc(&c->scanTicket, 1));
   if (ok) A(cudaMemcpy(c->position, pos4, 16 * N, cudaMemcpyHostToDevice));   // owOpenCLSolver.cpp:65

@@ -35,8 +35,6 @@ struct sph_ctx {
   unsigned *cellList;          // non-empty cells of this step (order arbitrary)
   unsigned *cellListCount;
   unsigned *cellCursor;        // work cursor of the tiled neighbour search
-  unsigned *fnMasks;           // N rows of 32 hit-mask words (P1 -> P2 of the neighbour search)
-  unsigned char *fnFlags;      // N: 1 = neighbourhood too crowded for the mask tables, use the generic scan
   int numSMs;
   bool force_generic_neighbors; // SPH_GENERIC_NEIGHBORS=1: one-thread-per-particle search (debug / A-B)
   unsigned long long *scanState;  // decoupled look-back tile states

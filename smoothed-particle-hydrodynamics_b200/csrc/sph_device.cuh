@@ -37,6 +37,11 @@ struct DevParams {
   double del2W;                       // del2WviscosityCoefficient
   double massGradW;                   // sphFluid.cl:1194
   double closeThr;                    // 0.5*(hScaled/2), sphFluid.cl:1166
+  // binT[j] = smallest float d2 whose radial-histogram bin (int)(sqrtf(d2)*30/h) (sphFluid.cl:157-160) is >= j,
+  // found on the host by bisection over the float bit patterns with the same IEEE operations; binT[0] = 0,
+  // binT[31] = +inf. The bin of d2 is then max{j : binT[j] <= d2}, exactly, without sqrt/div per candidate.
+  float binT[SPH_RADIUS_SEGMENTS + 2];
+  float binScale;                     // 30/h, for the approximate first guess of the bin
 };
 
 // ---- float4 lane-wise helpers (OpenCL vector semantics, one IEEE op per lane) ----

@@ -129,57 +129,76 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 }
 
 // ---------------------------------------------------------------- tiled path (the product path)
-// Two kernels.
-//
-// P1  k_neighbor_masks — one CTA per non-empty hash cell ("home cell"). All particles of a cell that
-//     sit in the same octant of it visit the same 8 cells in the same order (sphFluid.cl:248-308), so
-//     the home particles are grouped by octant and the group's candidates are the concatenation of
-//     those 8 cells ("virtual candidate list", 32-candidate chunks). A warp takes one PAIR of home
-//     particles, keeps the pair's coordinates in registers as fp32x2 operands and sweeps the chunks:
-//     lanes hold candidates (one float4 load each), the squared distances of both home particles come
-//     out of Blackwell's packed fp32x2 pipe (add/mul/fma.rn.f32x2), two ballots give the 32-bit hit
-//     masks of the chunk, lane c keeps chunk c's masks, and at the end the warp writes each particle's
-//     mask row with one coalesced store. The test is a conservative FILTER (radius 31h/30 — the largest
-//     r_thr the reference can choose — slightly inflated, FMA allowed): nothing inexact reaches the output.
-// P2  k_neighbor_select — one thread per particle walks its mask row in the reference's scan order,
-//     re-derives the exact distance of the ~35 hits with the reference's operation order, builds the
-//     30-bin radial histogram, picks r_thr (sphFluid.cl:310-324), keeps the first 32 hits within it
-//     (:166-174) and accumulates rho(t) (pcisph_computeDensity, :472-518) on them. The two scan passes
-//     of the reference become one sweep over the candidates plus two passes over the hits.
-// Particles whose neighbourhood does not fit the tables (more than FN_LMAX candidates or FN_CAP hits)
-// take find_neighbors_one, the generic two-pass scan.
-#define FN_THREADS 128
-#define FN_WARPS (FN_THREADS / 32)
-#define FN_HB 64                 // home particles per batch
-#define FN_ROWS (FN_HB + 8)      // rows = home particles in group order, groups padded to even size
-#define FN_LMAX 768              // candidates per octant group (8 cells) held in the index table
-#define FN_ROWW 32               // mask words per particle row (128 B); FN_LMAX / 32 <= FN_ROWW
-#define FN_CAP 52                // hits kept per particle in P2
+// One kernel, k_neighbor_tiles. A CTA takes a HOME BLOCK = the two hash cells (2b, 2b+1), whose
+// particles are one contiguous range of the sorted arrays, and
+//   stage   copies the positions of the 4x3x3 = 36 surrounding cells (offsets -1..2 in id, -1..1 in
+//           y-row and z-slab, searchCell wrap included) into shared memory as SoA x/y/z: every
+//           candidate any home particle of the block can visit, read from HBM/L2 once, coalesced;
+//   group   sorts the home particles by (home cell, octant): all particles of a cell that sit in the
+//           same octant of it visit the same 8 cells in the same order (sphFluid.cl:248-308). Those 8
+//           cells are 4 RUNS of two id-adjacent cells, and a run is contiguous in the staging area;
+//   sweep   (P1) one warp per PAIR of home particles of a group: the pair's coordinates live in
+//           registers as fp32x2 operands, lanes hold 32 consecutive staged candidates of a run, both
+//           squared distances come out of Blackwell's packed fp32x2 pipe, two ballots give the
+//           32-bit hit masks of the chunk, lane w keeps mask word w, and the row of words goes to
+//           shared memory. The test is a conservative FILTER (radius 31h/30 — the largest r_thr the
+//           reference can choose — slightly inflated, FMA allowed): nothing inexact reaches the output;
+//   select  (P2) one thread per home particle walks the bit ranges of its 8 cells in the reference's
+//           visiting order, re-derives the exact distance of the ~35 hits with the reference's
+//           operation order (from the staged copies), builds the 30-bin radial histogram, picks r_thr
+//           (sphFluid.cl:310-324), keeps the first 32 hits within it (:166-174), accumulates rho(t) on
+//           them (pcisph_computeDensity, :472-518) and writes the ids in the 32x32 tile layout.
+// The two scan passes of the reference (2 x ~512 candidates per particle) become one packed sweep plus
+// two passes over the hits; the mask rows never leave the SM. Particles whose neighbourhood does not fit
+// the tables (staging area, FT_NCH mask words, FT_CAP hits) take find_neighbors_one, the generic scan.
+#define FT_THREADS 128
+#define FT_WARPS (FT_THREADS / 32)
+#define FT_ROWS FT_THREADS        // home particles per batch (thread t of P2 owns particle b0 + t)
+#define FT_GROUPS 16              // (home cell 0/1) x octant
+#define FT_ROWPAD (FT_ROWS + FT_GROUPS)  // rows in group order, every group padded to an even size
+#define FT_NCELL 36               // staged cells: id offset hx in [-1,2], y-row and z-slab offsets in [-1,1]
+#define FT_CMAX 2816              // staged candidates (36 cells x 78); staged indices fit 12 bits
+#define FT_NCH 32                 // mask words per row: one per lane of the sweeping warp
+#define FT_MSTRIDE (FT_NCH + 1)   // odd row stride: P2's per-thread row walks are bank-conflict free; a row
+                                  // is reused for the 32 selected ids once its masks have been consumed
+#define FT_CAP 48                 // hits kept per particle in P2
 
-struct FnShared {
-  float2 px[FN_ROWS / 2], py[FN_ROWS / 2], pz[FN_ROWS / 2];
-  int rowId[FN_ROWS];
-  int cidx[8][FN_LMAX];
-  int cellB[27], cellN[27];
-  int cum[8][9], cbase[8][8];
-  int grpStart[9], grpCount[8], pairStart[9], bad[8];
-  int nextCell;
+struct FtShared {
+  float X[FT_CMAX + 32], Y[FT_CMAX + 32], Z[FT_CMAX + 32];  // +32: a run's last chunk may read past its end
+  unsigned masks[FT_ROWPAD * FT_MSTRIDE];
+  unsigned short hits[FT_CAP][FT_THREADS];   // (k << 12) | staged index, scan order
+  unsigned char hist[SPH_RADIUS_SEGMENTS + 2][FT_THREADS];
+  float2 px[FT_ROWPAD / 2], py[FT_ROWPAD / 2], pz[FT_ROWPAD / 2];
+  unsigned word[FT_GROUPS][FT_NCH];  // mask word w of a group: staged index of its bit 0 | (valid bits - 1) << 16
+  int bitLo[FT_GROUPS][8];           // cell k (reference visiting order) = bits [bitLo, bitLo + cntK) of the row
+  int cntK[FT_GROUPS][8];
+  int sB[FT_GROUPS][8];              // staged index of the cell's first particle
+  int dG[FT_GROUPS][8];              // staged index + dG = sorted particle id
+  int nWords[FT_GROUPS];
+  float binT[SPH_RADIUS_SEGMENTS + 2];
+  int gStart[FT_NCELL], cnt[FT_NCELL], sStart[FT_NCELL + 1];
+  int grpCount[FT_GROUPS], grpStart[FT_GROUPS], pairStart[FT_GROUPS + 1], bad[FT_GROUPS];
+  unsigned char pairGroup[FT_ROWPAD / 2];
+  int nextCell, blockBad;
 };
 
-template <int DUMMY>
-__global__ void __launch_bounds__(FN_THREADS) k_neighbor_masks(DevParams d, const float4 *__restrict__ sp,
-                                                               const unsigned *__restrict__ cellStart,
-                                                               const unsigned *__restrict__ cellList,
-                                                               const unsigned *__restrict__ cellListCount,
-                                                               unsigned *__restrict__ cellCursor,
-                                                               unsigned *__restrict__ masks,
-                                                               unsigned char *__restrict__ flags) {
-  __shared__ FnShared S;
+template <bool WITH_DENSITY>
+__global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, const float4 *__restrict__ sp,
+                                                                  const unsigned *__restrict__ cellStart,
+                                                                  const unsigned *__restrict__ cellList,
+                                                                  const unsigned *__restrict__ cellListCount,
+                                                                  unsigned *__restrict__ cellCursor,
+                                                                  int *__restrict__ nb, float *__restrict__ rho) {
+  extern __shared__ __align__(16) unsigned char ft_smem[];
+  FtShared &S = *reinterpret_cast<FtShared *>(ft_smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nCells = (int)*cellListCount;
   const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr (j == 30)
   const float rfilt2 = rmaxf * rmaxf * 1.0001f;
   const float FAR = 1.0e30f;
+  const float h2 = d.h * d.h;
+  if (tid < SPH_RADIUS_SEGMENTS + 2) S.binT[tid] = d.binT[tid];
+  for (int i = tid; i < 32; i += FT_THREADS) { S.X[FT_CMAX + i] = FAR; S.Y[FT_CMAX + i] = FAR; S.Z[FT_CMAX + i] = FAR; }
   while (true) {
     __syncthreads();
     if (tid == 0) S.nextCell = (int)atomicAdd(cellCursor, 1u);
@@ -187,23 +206,73 @@ __global__ void __launch_bounds__(FN_THREADS) k_neighbor_masks(DevParams d, cons
     const int ci = S.nextCell;
     if (ci >= nCells) break;
     const int cell = (int)cellList[ci];
-    const int cbeg = (int)cellStart[cell], cend = (int)cellStart[cell + 1];
-    if (tid < 27) {  // ranges of the 27 surrounding cells (searchCell wrap, sphFluid.cl:108-110)
-      int ox = tid % 3 - 1, oy = (tid / 3) % 3 - 1, oz = tid / 9 - 1;
-      int nc = search_cell(cell, ox + oy * d.gx + oz * d.gx * d.gy, d.G);
-      int b = (int)cellStart[nc];
-      S.cellB[tid] = b;
-      S.cellN[tid] = (int)cellStart[nc + 1] - b;
+    const int base = cell & ~1;
+    // every non-empty cell appears once in cellList; the block is run by its first non-empty cell
+    if (cell != base && cellStart[base + 1] != cellStart[base]) continue;
+    const int hBeg = (int)cellStart[base];
+    const int hMid = (int)cellStart[base + 1];
+    const int hEnd = (int)cellStart[min(base + 2, d.G)];
+    // ---- stage: ranges of the 36 surrounding cells, prefix of their sizes, then the positions
+    if (warp == 0) {
+      int c0 = 0, c1 = 0;
+      {
+        const int t = lane;
+        const int nc = search_cell(base, (t & 3) - 1 + ((t >> 2) % 3 - 1) * d.gx + (t / 12 - 1) * d.gx * d.gy, d.G);
+        const int b = (int)cellStart[nc];
+        c0 = (int)cellStart[nc + 1] - b;
+        S.gStart[t] = b;
+        S.cnt[t] = c0;
+      }
+      if (lane < FT_NCELL - 32) {
+        const int t = 32 + lane;
+        const int nc = search_cell(base, (t & 3) - 1 + ((t >> 2) % 3 - 1) * d.gx + (t / 12 - 1) * d.gx * d.gy, d.G);
+        const int b = (int)cellStart[nc];
+        c1 = (int)cellStart[nc + 1] - b;
+        S.gStart[t] = b;
+        S.cnt[t] = c1;
+      }
+      int inc = c0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+      }
+      const int tot32 = __shfl_sync(0xffffffffu, inc, 31);
+      S.sStart[lane] = inc - c0;
+      int inc1 = c1;
+#pragma unroll
+      for (int o = 1; o < 4; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, inc1, o);
+        if (lane >= o) inc1 += u;
+      }
+      if (lane < FT_NCELL - 32) S.sStart[32 + lane] = tot32 + inc1 - c1;
+      if (lane == FT_NCELL - 32 - 1) {
+        S.sStart[FT_NCELL] = tot32 + inc1;
+        S.blockBad = (tot32 + inc1 > FT_CMAX) ? 1 : 0;
+      }
     }
-    for (int b0 = cbeg; b0 < cend; b0 += FN_HB) {
-      const int hb = min(FN_HB, cend - b0);
+    __syncthreads();
+    const int blockBad = S.blockBad;
+    if (!blockBad) {
+#pragma unroll 1
+      for (int t = warp; t < FT_NCELL; t += FT_WARPS) {
+        const int g0 = S.gStart[t], n = S.cnt[t], s0 = S.sStart[t];
+        for (int i = lane; i < n; i += 32) {
+          const float4 q = ldg4(sp + g0 + i);
+          S.X[s0 + i] = q.x; S.Y[s0 + i] = q.y; S.Z[s0 + i] = q.z;
+        }
+      }
+    }
+    for (int b0 = hBeg; b0 < hEnd; b0 += FT_ROWS) {
+      const int hb = min(FT_ROWS, hEnd - b0);
       const int id = b0 + tid;
       __syncthreads();
-      if (tid < 8) S.grpCount[tid] = 0;
-      if (tid < FN_ROWS) S.rowId[tid] = -1;
-      if (tid < FN_ROWS / 2) { S.px[tid] = make_float2(FAR, FAR); S.py[tid] = make_float2(FAR, FAR); S.pz[tid] = make_float2(FAR, FAR); }
+      if (tid < FT_GROUPS) S.grpCount[tid] = 0;
+      for (int r = tid; r < FT_ROWPAD / 2; r += FT_THREADS) {
+        S.px[r] = make_float2(FAR, FAR); S.py[r] = make_float2(FAR, FAR); S.pz[r] = make_float2(FAR, FAR);
+      }
       __syncthreads();
-      // ---- group the home particles by octant (which half of the 2h cell, per axis: :253-271)
+      // ---- group the home particles by (home cell, octant); octant = which half of the 2h cell, per axis (:253-271)
       float4 pos = f4(0.f, 0.f, 0.f, 0.f);
       int g = 0, rankInG = 0;
       if (tid < hb) {
@@ -212,198 +281,176 @@ __global__ void __launch_bounds__(FN_THREADS) k_neighbor_masks(DevParams d, cons
         float cfy = (float)(int)(pos.y * d.cellSizeInv) * d.cellSize;
         float cfz = (float)(int)(pos.z * d.cellSizeInv) * d.cellSize;
         g = ((((pos.x - d.xmin) - cfx) < d.h) ? 0 : 1) | ((((pos.y - d.ymin) - cfy) < d.h) ? 0 : 2) |
-            ((((pos.z - d.zmin) - cfz) < d.h) ? 0 : 4);
+            ((((pos.z - d.zmin) - cfz) < d.h) ? 0 : 4) | ((id >= hMid) ? 8 : 0);
         rankInG = atomicAdd(&S.grpCount[g], 1);
       }
       __syncthreads();
-      if (tid < 8) {  // tables of group `tid`: its 8 cells in the reference's visiting order (:248-308)
+      if (tid < FT_GROUPS) {  // tables of group `tid`
         int gs = 0, ps = 0;
         for (int q = 0; q < tid; q++) { gs += (S.grpCount[q] + 1) & ~1; ps += (S.grpCount[q] + 1) >> 1; }
+        const int np = (S.grpCount[tid] + 1) >> 1;
         S.grpStart[tid] = gs;
         S.pairStart[tid] = ps;
-        if (tid == 7) S.pairStart[8] = ps + ((S.grpCount[7] + 1) >> 1);
-        const int sx = (tid & 1) ? 1 : -1, sy = (tid & 2) ? 1 : -1, sz = (tid & 4) ? 1 : -1;
-        int L = 0;
+        if (tid == FT_GROUPS - 1) S.pairStart[FT_GROUPS] = ps + np;
+        for (int q = 0; q < np; q++) S.pairGroup[ps + q] = (unsigned char)tid;
+        const int sx = (tid & 1) ? 1 : -1, sy = (tid & 2) ? 1 : -1, sz = (tid & 4) ? 1 : -1, hc = tid >> 3;
+        const int hxlo = hc + ((sx < 0) ? -1 : 0);  // the group's two id-adjacent cells are hxlo, hxlo + 1
+        // the 4 runs, ordered (0,0), (sy,0), (0,sz), (sy,sz): mask words of the row
+        int wOff[5];
+        int w = 0;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+          const int oy = (r & 1) ? sy : 0, oz = (r & 2) ? sz : 0;
+          const int tlo = (hxlo + 1) + (oy + 1) * 4 + (oz + 1) * 12;
+          const int s0 = S.sStart[tlo], len = S.cnt[tlo] + S.cnt[tlo + 1];
+          wOff[r] = w;
+          for (int c = 0; c * 32 < len; c++) {
+            const int nv = min(32, len - c * 32);
+            if (w < FT_NCH) S.word[tid][w] = (unsigned)(s0 + c * 32) | ((unsigned)(nv - 1) << 16);
+            w++;
+          }
+        }
+        wOff[4] = w;
+        S.nWords[tid] = w;
+        S.bad[tid] = (blockBad || w > FT_NCH) ? 1 : 0;
+        // the 8 cells in the reference's visiting order (:248-308): own, x, y, z, xy, xz, yz, xyz
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-          const int kx = (0xB2 >> k) & 1, ky = (0xD4 >> k) & 1, kz = (0xE8 >> k) & 1;  // own,x,y,z,xy,xz,yz,xyz
-          const int i27 = (kx * sx + 1) + (ky * sy + 1) * 3 + (kz * sz + 1) * 9;
-          S.cum[tid][k] = L;
-          S.cbase[tid][k] = S.cellB[i27];
-          L += S.cellN[i27];
+          const int kx = (0xB2 >> k) & 1, ky = (0xD4 >> k) & 1, kz = (0xE8 >> k) & 1;
+          const int hx = hc + kx * sx;
+          const int t = (hx + 1) + (ky * sy + 1) * 4 + (kz * sz + 1) * 12;
+          const int r = ky + 2 * kz;
+          S.bitLo[tid][k] = wOff[r] * 32 + ((hx == hxlo) ? 0 : S.cnt[t - 1]);
+          S.cntK[tid][k] = S.cnt[t];
+          S.sB[tid][k] = S.sStart[t];
+          S.dG[tid][k] = S.gStart[t] - S.sStart[t];
         }
-        S.cum[tid][8] = L;
-        S.bad[tid] = (L > FN_LMAX) ? 1 : 0;
       }
       __syncthreads();
+      int row = 0;
       if (tid < hb) {
-        const int row = S.grpStart[g] + rankInG;
+        row = S.grpStart[g] + rankInG;
         ((float *)S.px)[row] = pos.x; ((float *)S.py)[row] = pos.y; ((float *)S.pz)[row] = pos.z;
-        S.rowId[row] = id;
-        flags[id] = (unsigned char)S.bad[g];
-      }
-      // ---- virtual candidate list -> sorted index, per group
-#pragma unroll 1
-      for (int gg = 0; gg < 8; gg++) {
-        if (!S.grpCount[gg] || S.bad[gg]) continue;
-        const int L = S.cum[gg][8];
-        for (int v = tid; v < L; v += FN_THREADS) {
-          int k = 0;
-#pragma unroll
-          for (int q = 1; q < 8; q++) k += (v >= S.cum[gg][q]) ? 1 : 0;
-          S.cidx[gg][v] = S.cbase[gg][k] + v - S.cum[gg][k];
-        }
       }
       __syncthreads();
-      // ---- one warp per home pair: sweep the chunks
-      const int totalPairs = S.pairStart[8];
+      // ---- P1 sweep: one warp per home pair
+      const int totalPairs = S.pairStart[FT_GROUPS];
 #pragma unroll 1
-      for (int t = warp; t < totalPairs; t += FN_WARPS) {
-        int gg = 0;
-#pragma unroll
-        for (int q = 1; q < 8; q++) gg += (t >= S.pairStart[q]) ? 1 : 0;
+      for (int t = warp; t < totalPairs; t += FT_WARPS) {
+        const int gg = S.pairGroup[t];
         if (S.bad[gg]) continue;
         const int pr = (S.grpStart[gg] >> 1) + (t - S.pairStart[gg]);
         const float2 hx = S.px[pr], hy = S.py[pr], hz = S.pz[pr];
-        const int L = S.cum[gg][8];
-        const int nch = (L + 31) >> 5;
+        const unsigned *wtab = S.word[gg];
+        const int nch = S.nWords[gg];
         unsigned keep0 = 0, keep1 = 0;
-#pragma unroll 2
+#pragma unroll 4
         for (int c = 0; c < nch; c++) {
-          const int v = (c << 5) + lane;
-          float4 cd = f4(FAR, FAR, FAR, 0.f);
-          if (v < L) cd = ldg4(sp + S.cidx[gg][v]);
-          const float2 ncx = make_float2(-cd.x, -cd.x), ncy = make_float2(-cd.y, -cd.y), ncz = make_float2(-cd.z, -cd.z);
+          const unsigned wd = wtab[c];
+          const int s = (int)(wd & 0xffffu) + lane;
+          const unsigned valid = 0xffffffffu >> (31u - (wd >> 16));
+          const float cx = S.X[s], cy = S.Y[s], cz = S.Z[s];
+          const float2 ncx = make_float2(-cx, -cx), ncy = make_float2(-cy, -cy), ncz = make_float2(-cz, -cz);
           float2 ex = __fadd2_rn(hx, ncx), ey = __fadd2_rn(hy, ncy), ez = __fadd2_rn(hz, ncz);
           float2 dd = __ffma2_rn(ez, ez, __ffma2_rn(ey, ey, __fmul2_rn(ex, ex)));
-          const unsigned m0 = __ballot_sync(0xffffffffu, dd.x <= rfilt2);
-          const unsigned m1 = __ballot_sync(0xffffffffu, dd.y <= rfilt2);
+          const unsigned m0 = __ballot_sync(0xffffffffu, dd.x <= rfilt2) & valid;
+          const unsigned m1 = __ballot_sync(0xffffffffu, dd.y <= rfilt2) & valid;
           if (lane == c) { keep0 = m0; keep1 = m1; }
         }
-        const int id0 = S.rowId[2 * pr], id1 = S.rowId[2 * pr + 1];
         if (lane < nch) {
-          masks[(size_t)id0 * FN_ROWW + lane] = keep0;
-          if (id1 >= 0) masks[(size_t)id1 * FN_ROWW + lane] = keep1;
+          S.masks[(2 * pr) * FT_MSTRIDE + lane] = keep0;
+          S.masks[(2 * pr + 1) * FT_MSTRIDE + lane] = keep1;
         }
       }
-    }
-  }
-}
-
-struct FnSelShared {
-  int hits[FN_CAP][FN_THREADS];
-  int cumS[9][FN_THREADS];
-  int adjS[8][FN_THREADS];
-  unsigned char hist[SPH_RADIUS_SEGMENTS + 2][FN_THREADS];
-};
-
-template <bool WITH_DENSITY>
-__global__ void __launch_bounds__(FN_THREADS) k_neighbor_select(DevParams d, const float4 *__restrict__ sp,
-                                                                const unsigned *__restrict__ cellStart,
-                                                                const unsigned *__restrict__ masks,
-                                                                const unsigned char *__restrict__ flags,
-                                                                int *__restrict__ nb, float *__restrict__ rho) {
-  __shared__ FnSelShared S;
-  const int tid = threadIdx.x;
-  const int id = blockIdx.x * FN_THREADS + tid;
-  if (id >= d.N) return;
-  if (flags[id]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); return; }
-  const float4 pos = sp[id];
-  const float h2 = d.h * d.h;
-  {  // the 8 cells of this particle and the prefix of their sizes (virtual candidate index space)
-    int cells[8];
-    neighbor_cells(d, pos, (int)pos.w & d.mask, cells);
-    int L = 0;
+      __syncthreads();
+      // ---- P2 select: one thread per home particle
+      if (tid >= hb) continue;
+      if (S.bad[g]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
+      unsigned *mrow = S.masks + row * FT_MSTRIDE;
+      // bit ranges of the 8 cells, in visiting order -> hit list (scan order)
+      int nh = 0;
+#pragma unroll 1
+      for (int k = 0; k < 8; k++) {
+        const int n = S.cntK[g][k];
+        if (n == 0) continue;
+        const int lo = S.bitLo[g][k], hi = lo + n;  // [lo, hi)
+        const int sOff = S.sB[g][k] - lo;           // bit position + sOff = staged index
+        const int self = id - S.dG[g][k] - sOff;    // bit position of this particle, if it lies in this cell
+        const unsigned tag = (unsigned)k << 12;
+        int c = lo >> 5;
+        const int cLast = (hi - 1) >> 5;
+        unsigned m = mrow[c] & (0xffffffffu << (lo & 31));
+        while (true) {
+          if (c == cLast) m &= 0xffffffffu >> (31 - ((hi - 1) & 31));
+          while (m) {
+            const int bit = (c << 5) + __ffs(m) - 1;
+            m &= m - 1;
+            if (bit != self) {
+              if (nh < FT_CAP) S.hits[nh][tid] = (unsigned short)(tag | (unsigned)(bit + sOff));
+              nh++;
+            }
+          }
+          if (c == cLast) break;
+          m = mrow[++c];
+        }
+      }
+      if (nh > FT_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-      const int b = (int)cellStart[cells[k]], n = (int)cellStart[cells[k] + 1] - b;
-      S.cumS[k][tid] = L;
-      S.adjS[k][tid] = b - L;
-      L += n;
-    }
-    S.cumS[8][tid] = L;
-  }
-  const int L = S.cumS[8][tid];
-  const int nch = (L + 31) >> 5;
-  // ---- mask row -> candidate list in scan order (each thread walks words and bits at its own pace)
-  const unsigned *row = masks + (size_t)id * FN_ROWW;
-  int nh = 0;
-  {
-    int c = 0, k = 0, kend = S.cumS[1][tid], adj = S.adjS[0][tid];
-    unsigned m = nch > 0 ? __ldg(row) : 0u;
-    while (true) {
-      if (m == 0u) {
-        if (++c >= nch) break;
-        m = __ldg(row + c);
-        continue;
-      }
-      const int v = (c << 5) + __ffs(m) - 1;
-      m &= m - 1;
-      while (v >= kend) { ++k; kend = S.cumS[k + 1][tid]; adj = S.adjS[k][tid]; }
-      const int cidx = v + adj;
-      if (cidx != id) {
-        if (nh < FN_CAP) S.hits[nh][tid] = cidx;
-        nh++;
-      }
-    }
-  }
-  if (nh > FN_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); return; }
-#pragma unroll
-  for (int b = 0; b < SPH_RADIUS_SEGMENTS; b++) S.hist[b][tid] = 0;
-  // ---- exact distances + 30-bin radial histogram of everything within h (:157-161)
-  {
-    float4 q = (nh > 0) ? ldg4(sp + S.hits[0][tid]) : pos;
-    for (int t = 0; t < nh; t++) {
-      const float4 cur = q;
-      if (t + 1 < nh) q = ldg4(sp + S.hits[t + 1][tid]);
-      float ex = pos.x - cur.x, ey = pos.y - cur.y, ez = pos.z - cur.z;
-      float dd = ex * ex + ey * ey + ez * ez;
-      if (dd <= h2) {
-        int b = (int)(sqrtf(dd) * SPH_RADIUS_SEGMENTS / d.h);
-        if (b < SPH_RADIUS_SEGMENTS) {
-          unsigned v = S.hist[b][tid];
-          if (v < 255u) S.hist[b][tid] = (unsigned char)(v + 1u);  // saturation keeps the >32 logic exact
+      for (int b = 0; b < SPH_RADIUS_SEGMENTS; b++) S.hist[b][tid] = 0;
+      // exact distances + 30-bin radial histogram of everything within h (:157-161)
+      for (int t = 0; t < nh; t++) {
+        const int s = S.hits[t][tid] & 0xfff;
+        float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
+        float dd = ex * ex + ey * ey + ez * ez;
+        if (dd <= h2) {
+          // bin (int)(sqrtf(dd)*30/h): approximate guess, made exact with the host-built thresholds
+          float sq;
+          asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
+          int e = (int)(sq * d.binScale);
+          e = min(e, SPH_RADIUS_SEGMENTS);
+          const int b = e + ((dd >= S.binT[e + 1]) ? 1 : 0) - ((dd < S.binT[e]) ? 1 : 0);
+          if (b < SPH_RADIUS_SEGMENTS) {
+            unsigned hv = S.hist[b][tid];
+            if (hv < 255u) S.hist[b][tid] = (unsigned char)(hv + 1u);  // saturation keeps the >32 logic exact
+          }
         }
       }
-    }
-  }
-  // ---- radius threshold (:310-324)
-  int j = 0, sum = 0;
-  while (j < SPH_RADIUS_SEGMENTS) {
-    sum += S.hist[j][tid];
-    if (sum == SPH_NB) break;
-    if (sum > SPH_NB) { j--; break; }
-    j++;
-  }
-  const float r_thr = (float)(j + 1) * d.h / SPH_RADIUS_SEGMENTS;
-  const float r2 = r_thr * r_thr;
-  // ---- first 32 hits within r_thr, in scan order (:166-174) + rho(t)
-  int found = 0;
-  double density = 0.0;
-  {
-    float4 q = (nh > 0) ? ldg4(sp + S.hits[0][tid]) : pos;
-    for (int t = 0; t < nh; t++) {
-      const float4 cur = q;
-      if (t + 1 < nh) q = ldg4(sp + S.hits[t + 1][tid]);
-      float ex = pos.x - cur.x, ey = pos.y - cur.y, ez = pos.z - cur.z;
-      float dd = ex * ex + ey * ey + ez * ez;
-      if (dd <= r2) {
-        S.hits[found][tid] = S.hits[t][tid];
-        if (WITH_DENSITY) {
-          float r = sqrtf(dd) * d.simScale;
-          float rr = r * r;
-          density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
-        }
-        if (++found == SPH_NB) break;
+      // radius threshold (:310-324)
+      int j = 0, sum = 0;
+      while (j < SPH_RADIUS_SEGMENTS) {
+        sum += S.hist[j][tid];
+        if (sum == SPH_NB) break;
+        if (sum > SPH_NB) { j--; break; }
+        j++;
       }
-    }
-  }
+      const float r_thr = (float)(j + 1) * d.h / SPH_RADIUS_SEGMENTS;
+      const float r2 = r_thr * r_thr;
+      // first 32 hits within r_thr, in scan order (:166-174) + rho(t)
+      int found = 0;
+      double density = 0.0;
+      for (int t = 0; t < nh; t++) {
+        const unsigned hv = S.hits[t][tid];
+        const int s = hv & 0xfff;
+        float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
+        float dd = ex * ex + ey * ey + ez * ez;
+        if (dd <= r2) {
+          mrow[found] = (unsigned)(s + S.dG[g][hv >> 12]);  // own row: its masks are consumed
+          if (WITH_DENSITY) {
+            float r = sqrtf(dd) * d.simScale;
+            float rr = r * r;
+            density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
+          }
+          if (++found == SPH_NB) break;
+        }
+      }
 #pragma unroll 8
-  for (int k = 0; k < SPH_NB; k++) nb[nb_index(id, k)] = (k < found) ? S.hits[k][tid] : SPH_NO_ID;
-  if (WITH_DENSITY) {
-    if (density < (double)d.hScaled6) density = (double)d.hScaled6;
-    density *= d.massWpoly6;
-    rho[id] = (float)density;
+      for (int q = 0; q < SPH_NB; q++) nb[nb_index(id, q)] = (q < found) ? (int)mrow[q] : SPH_NO_ID;
+      if (WITH_DENSITY) {
+        if (density < (double)d.hScaled6) density = (double)d.hScaled6;
+        density *= d.massWpoly6;
+        rho[id] = (float)density;
+      }
+    }
   }
 }
 
@@ -429,6 +476,21 @@ void launch_clear_neighbors(sph_ctx *c) {
   k_clear_neighbors<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->nbIds, n);
 }
 
+static int ft_ctas_per_sm = 0;
+template <bool WD>
+static void launch_tiles(sph_ctx *c) {
+  if (!ft_ctas_per_sm) {
+    cudaFuncSetAttribute(k_neighbor_tiles<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FtShared));
+    cudaFuncSetAttribute(k_neighbor_tiles<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FtShared));
+    int occ = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_neighbor_tiles<true>, FT_THREADS, sizeof(FtShared));
+    ft_ctas_per_sm = occ < 1 ? 1 : occ;
+  }
+  cudaMemsetAsync(c->cellCursor, 0, sizeof(unsigned), c->stream);
+  k_neighbor_tiles<WD><<<c->numSMs * ft_ctas_per_sm, FT_THREADS, sizeof(FtShared), c->stream>>>(
+      c->d, c->sortedPosition, c->cellStart, c->cellList, c->cellListCount, c->cellCursor, c->nbIds, c->rho);
+}
+
 void launch_find_neighbors(sph_ctx *c, bool with_density) {
   if (c->force_generic_neighbors) {
     int blocks = (c->d.N + 127) / 128;
@@ -438,26 +500,9 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
       k_find_neighbors_generic<false><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho);
     return;
   }
-  // P1: persistent CTAs (one resident wave), cells handed out through an atomic cursor; P2: one thread per particle
-  static int occ = 0;
-  if (!occ) {
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_neighbor_masks<0>, FN_THREADS, 0);
-    if (occ < 1) occ = 1;
-  }
-  cudaMemsetAsync(c->cellCursor, 0, sizeof(unsigned), c->stream);
-  k_neighbor_masks<0><<<c->numSMs * occ, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->cellList,
-                                                                   c->cellListCount, c->cellCursor, c->fnMasks,
-                                                                   c->fnFlags);
-  const int blocks = (c->d.N + FN_THREADS - 1) / FN_THREADS;
-  if (with_density)
-    k_neighbor_select<true><<<blocks, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->fnMasks,
-                                                                 c->fnFlags, c->nbIds, c->rho);
-  else
-    k_neighbor_select<false><<<blocks, FN_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->fnMasks,
-                                                                  c->fnFlags, c->nbIds, c->rho);
+  // persistent CTAs (one resident wave); home blocks handed out through an atomic cursor over cellList
+  if (with_density) launch_tiles<true>(c); else launch_tiles<false>(c);
 }
-
-size_t sph_neighbor_mask_words(size_t n) { return n * FN_ROWW; }
 
 void launch_materialize_neighbor_map(sph_ctx *c, float2 *out) {
   size_t n = (size_t)c->d.N * SPH_NB;
