@@ -32,7 +32,7 @@ struct sph_ctx {
   float *sortedType;           // N type tag (position.w) in sorted order
   float4 *spT;                 // N sorted (x, y, z, type tag): the copy the force kernels gather
   float2 *prs;                 // N packed (pressure, rho*) of the fused PCISPH loop
-  unsigned *cellList;          // non-empty cells of this step (order arbitrary)
+  unsigned *cellList;          // first non-empty cell of every home block (cell pair) of this step (order arbitrary)
   unsigned *cellListCount;
   unsigned *cellCursor;        // work cursor of the tiled neighbour search
   int numSMs;

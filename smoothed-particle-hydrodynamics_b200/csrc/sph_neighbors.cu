@@ -129,8 +129,8 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 }
 
 // ---------------------------------------------------------------- tiled path (the product path)
-// One kernel, k_neighbor_tiles. A CTA takes a HOME BLOCK = the two hash cells (2b, 2b+1), whose
-// particles are one contiguous range of the sorted arrays, and
+// One persistent kernel, k_neighbor_tiles. A CTA takes a HOME BLOCK = the two hash cells (2b, 2b+1),
+// whose particles are one contiguous range of the sorted arrays, and
 //   stage   copies the positions of the 4x3x3 = 36 surrounding cells (offsets -1..2 in id, -1..1 in
 //           y-row and z-slab, searchCell wrap included) into shared memory as SoA x/y/z: every
 //           candidate any home particle of the block can visit, read from HBM/L2 once, coalesced;
@@ -143,43 +143,135 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 //           32-bit hit masks of the chunk, lane w keeps mask word w, and the row of words goes to
 //           shared memory. The test is a conservative FILTER (radius 31h/30 — the largest r_thr the
 //           reference can choose — slightly inflated, FMA allowed): nothing inexact reaches the output;
-//   select  (P2) one thread per home particle walks the bit ranges of its 8 cells in the reference's
-//           visiting order, re-derives the exact distance of the ~35 hits with the reference's
+//   select  (P2) one thread per home particle walks its row through the group's SEGMENT table (one
+//           segment = the bits of one mask word that belong to one cell, listed in the reference's
+//           visiting order), re-derives the exact distance of the ~35 hits with the reference's
 //           operation order (from the staged copies), builds the 30-bin radial histogram, picks r_thr
 //           (sphFluid.cl:310-324), keeps the first 32 hits within it (:166-174), accumulates rho(t) on
 //           them (pcisph_computeDensity, :472-518) and writes the ids in the 32x32 tile layout.
 // The two scan passes of the reference (2 x ~512 candidates per particle) become one packed sweep plus
-// two passes over the hits; the mask rows never leave the SM. Particles whose neighbourhood does not fit
-// the tables (staging area, FT_NCH mask words, FT_CAP hits) take find_neighbors_one, the generic scan.
-#define FT_THREADS 128
+// two passes over the hits; the mask rows never leave the SM. While a block is swept, warp 0 fetches the
+// next block's cell table, so the cursor atomic and the cellStart loads are off the critical path.
+// Particles whose neighbourhood does not fit the tables (staging area, FT_NCH mask words, FT_NSEG
+// segments, FT_CAP hits) take find_neighbors_one, the generic scan.
+#define FT_THREADS 160
 #define FT_WARPS (FT_THREADS / 32)
 #define FT_ROWS FT_THREADS        // home particles per batch (thread t of P2 owns particle b0 + t)
 #define FT_GROUPS 16              // (home cell 0/1) x octant
 #define FT_ROWPAD (FT_ROWS + FT_GROUPS)  // rows in group order, every group padded to an even size
 #define FT_NCELL 36               // staged cells: id offset hx in [-1,2], y-row and z-slab offsets in [-1,1]
-#define FT_CMAX 2816              // staged candidates (36 cells x 78); staged indices fit 12 bits
-#define FT_NCH 32                 // mask words per row: one per lane of the sweeping warp
-#define FT_MSTRIDE (FT_NCH + 1)   // odd row stride: P2's per-thread row walks are bank-conflict free; a row
-                                  // is reused for the 32 selected ids once its masks have been consumed
+#define FT_CMAX 2560              // staged candidates (36 cells x 71); staged indices fit 12 bits
+#define FT_NCH 24                 // mask words per row (<= 32: lane w of the sweeping warp keeps word w)
+#define FT_MSTRIDE (FT_NCH + 1)   // odd row stride: P2's per-thread row walks are bank-conflict free
+#define FT_NSEG 32                // segments per group
 #define FT_CAP 48                 // hits kept per particle in P2
+
+struct FtHalo {                   // cell table of one home block
+  int gStart[FT_NCELL], cnt[FT_NCELL], sStart[FT_NCELL + 1];
+  int hBeg, hMid, hEnd, bad, valid;
+};
 
 struct FtShared {
   float X[FT_CMAX + 32], Y[FT_CMAX + 32], Z[FT_CMAX + 32];  // +32: a run's last chunk may read past its end
   unsigned masks[FT_ROWPAD * FT_MSTRIDE];
   unsigned short hits[FT_CAP][FT_THREADS];   // (k << 12) | staged index, scan order
-  unsigned char hist[SPH_RADIUS_SEGMENTS + 2][FT_THREADS];
   float2 px[FT_ROWPAD / 2], py[FT_ROWPAD / 2], pz[FT_ROWPAD / 2];
-  unsigned word[FT_GROUPS][FT_NCH];  // mask word w of a group: staged index of its bit 0 | (valid bits - 1) << 16
-  int bitLo[FT_GROUPS][8];           // cell k (reference visiting order) = bits [bitLo, bitLo + cntK) of the row
-  int cntK[FT_GROUPS][8];
-  int sB[FT_GROUPS][8];              // staged index of the cell's first particle
-  int dG[FT_GROUPS][8];              // staged index + dG = sorted particle id
-  int nWords[FT_GROUPS];
+  unsigned short wordOff[FT_GROUPS][FT_NCH];  // mask word w of a group: byte offset of its bit-0 candidate in X/Y/Z
+  unsigned wordValid[FT_GROUPS][FT_NCH]; // ... and which of its 32 bits are real candidates
+  unsigned segMask[FT_GROUPS][FT_NSEG];  // segment: bits of mask word (info >> 16) that belong to cell k
+  unsigned segInfo[FT_GROUPS][FT_NSEG];  // (staged index of bit 0 + 32) | k << 13 | word << 16
+  int dG[FT_GROUPS][8];                  // staged index + dG = sorted particle id, per visited cell k
+  int nWords[FT_GROUPS], nSeg[FT_GROUPS], bad[FT_GROUPS];
   float binT[SPH_RADIUS_SEGMENTS + 2];
-  int gStart[FT_NCELL], cnt[FT_NCELL], sStart[FT_NCELL + 1];
-  int grpCount[FT_GROUPS], grpStart[FT_GROUPS], pairStart[FT_GROUPS + 1], bad[FT_GROUPS];
+  FtHalo halo[2];
+  int grpCount[FT_GROUPS], grpStart[FT_GROUPS], pairStart[FT_GROUPS + 1];
   unsigned char pairGroup[FT_ROWPAD / 2];
-  int nextCell, blockBad;
+  int pairCursor;
+};
+
+// warp-level: take the next home block from the work list and build its cell table
+__device__ __forceinline__ void ft_fetch_block(const DevParams &d, FtHalo &H, const unsigned *__restrict__ cellStart,
+                                               const unsigned *__restrict__ cellList, int nBlocks,
+                                               unsigned *__restrict__ cellCursor, int lane) {
+  int ci = 0;
+  if (lane == 0) ci = (int)atomicAdd(cellCursor, 1u);
+  ci = __shfl_sync(0xffffffffu, ci, 0);
+  if (ci >= nBlocks) {
+    if (lane == 0) H.valid = 0;
+    return;
+  }
+  const int base = (int)cellList[ci] & ~1;
+  int c0 = 0, c1 = 0;
+  {
+    const int t = lane;
+    const int nc = search_cell(base, (t & 3) - 1 + ((t >> 2) % 3 - 1) * d.gx + (t / 12 - 1) * d.gx * d.gy, d.G);
+    const int b = (int)cellStart[nc];
+    c0 = (int)cellStart[nc + 1] - b;
+    H.gStart[t] = b;
+    H.cnt[t] = c0;
+  }
+  if (lane < FT_NCELL - 32) {
+    const int t = 32 + lane;
+    const int nc = search_cell(base, (t & 3) - 1 + ((t >> 2) % 3 - 1) * d.gx + (t / 12 - 1) * d.gx * d.gy, d.G);
+    const int b = (int)cellStart[nc];
+    c1 = (int)cellStart[nc + 1] - b;
+    H.gStart[t] = b;
+    H.cnt[t] = c1;
+  }
+  int inc = c0;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += u;
+  }
+  const int tot32 = __shfl_sync(0xffffffffu, inc, 31);
+  H.sStart[lane] = inc - c0;
+  int inc1 = c1;
+#pragma unroll
+  for (int o = 1; o < 4; o <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, inc1, o);
+    if (lane >= o) inc1 += u;
+  }
+  if (lane < FT_NCELL - 32) H.sStart[32 + lane] = tot32 + inc1 - c1;
+  if (lane == FT_NCELL - 32 - 1) {
+    H.sStart[FT_NCELL] = tot32 + inc1;
+    H.bad = (tot32 + inc1 > FT_CMAX) ? 1 : 0;
+  }
+  if (lane == 0) {
+    H.hBeg = (int)cellStart[base];
+    H.hMid = (int)cellStart[base + 1];
+    H.hEnd = (int)cellStart[min(base + 2, d.G)];
+    H.valid = 1;
+  }
+}
+
+// geometry of group g = (home cell hc, octant): its 4 runs, ordered (0,0), (sy,0), (0,sz), (sy,sz)
+struct FtGroupGeom {
+  int sx, sy, sz, hc, hxlo;
+  int wOff[5];  // first mask word of each run
+  __device__ __forceinline__ void init(int g, const FtHalo &H) {
+    sx = (g & 1) ? 1 : -1; sy = (g & 2) ? 1 : -1; sz = (g & 4) ? 1 : -1; hc = g >> 3;
+    hxlo = hc + ((sx < 0) ? -1 : 0);  // the group's two id-adjacent cells are hxlo, hxlo + 1
+    int w = 0;
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      const int tlo = run_slot(r);
+      wOff[r] = w;
+      w += (H.cnt[tlo] + H.cnt[tlo + 1] + 31) >> 5;
+    }
+    wOff[4] = w;
+  }
+  __device__ __forceinline__ int run_slot(int r) const {
+    const int oy = (r & 1) ? sy : 0, oz = (r & 2) ? sz : 0;
+    return (hxlo + 1) + (oy + 1) * 4 + (oz + 1) * 12;
+  }
+  // cell k in the reference's visiting order (:248-308): own, x, y, z, xy, xz, yz, xyz -> staged slot, first row bit
+  __device__ __forceinline__ void cell(int k, const FtHalo &H, int &t, int &lo) const {
+    const int kx = (0xB2 >> k) & 1, ky = (0xD4 >> k) & 1, kz = (0xE8 >> k) & 1;
+    const int hx = hc + kx * sx;
+    t = (hx + 1) + (ky * sy + 1) * 4 + (kz * sz + 1) * 12;
+    lo = wOff[ky + 2 * kz] * 32 + ((hx == hxlo) ? 0 : H.cnt[t - 1]);
+  }
 };
 
 template <bool WITH_DENSITY>
@@ -192,71 +284,75 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
   extern __shared__ __align__(16) unsigned char ft_smem[];
   FtShared &S = *reinterpret_cast<FtShared *>(ft_smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nCells = (int)*cellListCount;
+  const int nBlocks = (int)*cellListCount;
   const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr (j == 30)
   const float rfilt2 = rmaxf * rmaxf * 1.0001f;
   const float FAR = 1.0e30f;
   const float h2 = d.h * d.h;
   if (tid < SPH_RADIUS_SEGMENTS + 2) S.binT[tid] = d.binT[tid];
-  for (int i = tid; i < 32; i += FT_THREADS) { S.X[FT_CMAX + i] = FAR; S.Y[FT_CMAX + i] = FAR; S.Z[FT_CMAX + i] = FAR; }
+  if (tid < 32) { S.X[FT_CMAX + tid] = FAR; S.Y[FT_CMAX + tid] = FAR; S.Z[FT_CMAX + tid] = FAR; }
+  if (tid < FT_GROUPS) S.grpCount[tid] = 0;
+  if (tid == 0) S.pairCursor = 0;
+  for (int r = tid; r < FT_ROWPAD / 2; r += FT_THREADS) {
+    S.px[r] = make_float2(FAR, FAR); S.py[r] = make_float2(FAR, FAR); S.pz[r] = make_float2(FAR, FAR);
+  }
+  if (warp == 0) ft_fetch_block(d, S.halo[0], cellStart, cellList, nBlocks, cellCursor, lane);
+  int cur = 0;
   while (true) {
-    __syncthreads();
-    if (tid == 0) S.nextCell = (int)atomicAdd(cellCursor, 1u);
-    __syncthreads();
-    const int ci = S.nextCell;
-    if (ci >= nCells) break;
-    const int cell = (int)cellList[ci];
-    const int base = cell & ~1;
-    // every non-empty cell appears once in cellList; the block is run by its first non-empty cell
-    if (cell != base && cellStart[base + 1] != cellStart[base]) continue;
-    const int hBeg = (int)cellStart[base];
-    const int hMid = (int)cellStart[base + 1];
-    const int hEnd = (int)cellStart[min(base + 2, d.G)];
-    // ---- stage: ranges of the 36 surrounding cells, prefix of their sizes, then the positions
-    if (warp == 0) {
-      int c0 = 0, c1 = 0;
-      {
-        const int t = lane;
-        const int nc = search_cell(base, (t & 3) - 1 + ((t >> 2) % 3 - 1) * d.gx + (t / 12 - 1) * d.gx * d.gy, d.G);
-        const int b = (int)cellStart[nc];
-        c0 = (int)cellStart[nc + 1] - b;
-        S.gStart[t] = b;
-        S.cnt[t] = c0;
+    __syncthreads();  // (A) halo[cur] is ready; the previous block's P2 is over
+    const FtHalo &H = S.halo[cur];
+    if (!H.valid) break;
+    const int hBeg = H.hBeg, hMid = H.hMid, hEnd = H.hEnd, blockBad = H.bad;
+    // ---- group tables of the block (depend on the cell table only)
+    if (tid < FT_GROUPS * 4) {  // thread (g, r): the mask words of run r
+      const int g = tid >> 2, r = tid & 3;
+      FtGroupGeom q;
+      q.init(g, H);
+      const int tlo = q.run_slot(r);
+      const int s0 = H.sStart[tlo], len = H.cnt[tlo] + H.cnt[tlo + 1];
+      int w = q.wOff[r];
+      for (int c = 0; c * 32 < len; c++, w++) {
+        if (w < FT_NCH) {
+          S.wordOff[g][w] = (unsigned short)((s0 + c * 32) * 4);
+          S.wordValid[g][w] = 0xffffffffu >> (32 - min(32, len - c * 32));
+        }
       }
-      if (lane < FT_NCELL - 32) {
-        const int t = 32 + lane;
-        const int nc = search_cell(base, (t & 3) - 1 + ((t >> 2) % 3 - 1) * d.gx + (t / 12 - 1) * d.gx * d.gy, d.G);
-        const int b = (int)cellStart[nc];
-        c1 = (int)cellStart[nc + 1] - b;
-        S.gStart[t] = b;
-        S.cnt[t] = c1;
+      if (r == 3) S.nWords[g] = q.wOff[4];
+    }
+    if (tid < FT_GROUPS * 8) {  // thread (g, k): the segments of visited cell k
+      const int g = tid >> 3, k = tid & 7;
+      FtGroupGeom q;
+      q.init(g, H);
+      int sg = 0;
+      for (int kk = 0; kk < k; kk++) {
+        int t, lo;
+        q.cell(kk, H, t, lo);
+        const int n = H.cnt[t];
+        if (n) sg += ((lo + n - 1) >> 5) - (lo >> 5) + 1;
       }
-      int inc = c0;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int u = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += u;
+      int t, lo;
+      q.cell(k, H, t, lo);
+      const int n = H.cnt[t], hi = lo + n;
+      S.dG[g][k] = H.gStart[t] - H.sStart[t];
+      if (n) {
+        for (int w = lo >> 5; w <= (hi - 1) >> 5; w++, sg++) {
+          const int a = max(lo, w * 32) - w * 32, b = min(hi, w * 32 + 32) - w * 32;  // bits [a, b) of word w
+          if (sg < FT_NSEG) {
+            S.segMask[g][sg] = (0xffffffffu << a) & (0xffffffffu >> (32 - b));
+            S.segInfo[g][sg] = (unsigned)(H.sStart[t] - lo + w * 32 + 32) | ((unsigned)k << 13) | ((unsigned)w << 16);
+          }
+        }
       }
-      const int tot32 = __shfl_sync(0xffffffffu, inc, 31);
-      S.sStart[lane] = inc - c0;
-      int inc1 = c1;
-#pragma unroll
-      for (int o = 1; o < 4; o <<= 1) {
-        const int u = __shfl_up_sync(0xffffffffu, inc1, o);
-        if (lane >= o) inc1 += u;
-      }
-      if (lane < FT_NCELL - 32) S.sStart[32 + lane] = tot32 + inc1 - c1;
-      if (lane == FT_NCELL - 32 - 1) {
-        S.sStart[FT_NCELL] = tot32 + inc1;
-        S.blockBad = (tot32 + inc1 > FT_CMAX) ? 1 : 0;
+      if (k == 7) {
+        S.nSeg[g] = sg;
+        S.bad[g] = (blockBad || q.wOff[4] > FT_NCH || sg > FT_NSEG) ? 1 : 0;
       }
     }
-    __syncthreads();
-    const int blockBad = S.blockBad;
+    // ---- stage the positions of the 36 cells
     if (!blockBad) {
 #pragma unroll 1
       for (int t = warp; t < FT_NCELL; t += FT_WARPS) {
-        const int g0 = S.gStart[t], n = S.cnt[t], s0 = S.sStart[t];
+        const int g0 = H.gStart[t], n = H.cnt[t], s0 = H.sStart[t];
         for (int i = lane; i < n; i += 32) {
           const float4 q = ldg4(sp + g0 + i);
           S.X[s0 + i] = q.x; S.Y[s0 + i] = q.y; S.Z[s0 + i] = q.z;
@@ -266,12 +362,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
     for (int b0 = hBeg; b0 < hEnd; b0 += FT_ROWS) {
       const int hb = min(FT_ROWS, hEnd - b0);
       const int id = b0 + tid;
-      __syncthreads();
-      if (tid < FT_GROUPS) S.grpCount[tid] = 0;
-      for (int r = tid; r < FT_ROWPAD / 2; r += FT_THREADS) {
-        S.px[r] = make_float2(FAR, FAR); S.py[r] = make_float2(FAR, FAR); S.pz[r] = make_float2(FAR, FAR);
-      }
-      __syncthreads();
+      if (b0 != hBeg) __syncthreads();  // (A') the previous batch's P2 is over
       // ---- group the home particles by (home cell, octant); octant = which half of the 2h cell, per axis (:253-271)
       float4 pos = f4(0.f, 0.f, 0.f, 0.f);
       int g = 0, rankInG = 0;
@@ -284,144 +375,131 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
             ((((pos.z - d.zmin) - cfz) < d.h) ? 0 : 4) | ((id >= hMid) ? 8 : 0);
         rankInG = atomicAdd(&S.grpCount[g], 1);
       }
-      __syncthreads();
-      if (tid < FT_GROUPS) {  // tables of group `tid`
-        int gs = 0, ps = 0;
-        for (int q = 0; q < tid; q++) { gs += (S.grpCount[q] + 1) & ~1; ps += (S.grpCount[q] + 1) >> 1; }
+      __syncthreads();  // (C) group sizes are final; tables and staging are visible
+      int row = 0;
+      {
+        int gs = 0;
+#pragma unroll
+        for (int q = 0; q < FT_GROUPS; q++) gs += (q < g) ? ((S.grpCount[q] + 1) & ~1) : 0;
+        row = gs + rankInG;
+      }
+      if (tid < hb) { ((float *)S.px)[row] = pos.x; ((float *)S.py)[row] = pos.y; ((float *)S.pz)[row] = pos.z; }
+      if (tid < FT_GROUPS) {
+        int ps = 0;
+        for (int q = 0; q < tid; q++) ps += (S.grpCount[q] + 1) >> 1;
         const int np = (S.grpCount[tid] + 1) >> 1;
-        S.grpStart[tid] = gs;
+        S.grpStart[tid] = 2 * ps;
         S.pairStart[tid] = ps;
         if (tid == FT_GROUPS - 1) S.pairStart[FT_GROUPS] = ps + np;
         for (int q = 0; q < np; q++) S.pairGroup[ps + q] = (unsigned char)tid;
-        const int sx = (tid & 1) ? 1 : -1, sy = (tid & 2) ? 1 : -1, sz = (tid & 4) ? 1 : -1, hc = tid >> 3;
-        const int hxlo = hc + ((sx < 0) ? -1 : 0);  // the group's two id-adjacent cells are hxlo, hxlo + 1
-        // the 4 runs, ordered (0,0), (sy,0), (0,sz), (sy,sz): mask words of the row
-        int wOff[5];
-        int w = 0;
-#pragma unroll
-        for (int r = 0; r < 4; r++) {
-          const int oy = (r & 1) ? sy : 0, oz = (r & 2) ? sz : 0;
-          const int tlo = (hxlo + 1) + (oy + 1) * 4 + (oz + 1) * 12;
-          const int s0 = S.sStart[tlo], len = S.cnt[tlo] + S.cnt[tlo + 1];
-          wOff[r] = w;
-          for (int c = 0; c * 32 < len; c++) {
-            const int nv = min(32, len - c * 32);
-            if (w < FT_NCH) S.word[tid][w] = (unsigned)(s0 + c * 32) | ((unsigned)(nv - 1) << 16);
-            w++;
-          }
-        }
-        wOff[4] = w;
-        S.nWords[tid] = w;
-        S.bad[tid] = (blockBad || w > FT_NCH) ? 1 : 0;
-        // the 8 cells in the reference's visiting order (:248-308): own, x, y, z, xy, xz, yz, xyz
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-          const int kx = (0xB2 >> k) & 1, ky = (0xD4 >> k) & 1, kz = (0xE8 >> k) & 1;
-          const int hx = hc + kx * sx;
-          const int t = (hx + 1) + (ky * sy + 1) * 4 + (kz * sz + 1) * 12;
-          const int r = ky + 2 * kz;
-          S.bitLo[tid][k] = wOff[r] * 32 + ((hx == hxlo) ? 0 : S.cnt[t - 1]);
-          S.cntK[tid][k] = S.cnt[t];
-          S.sB[tid][k] = S.sStart[t];
-          S.dG[tid][k] = S.gStart[t] - S.sStart[t];
-        }
       }
-      __syncthreads();
-      int row = 0;
-      if (tid < hb) {
-        row = S.grpStart[g] + rankInG;
-        ((float *)S.px)[row] = pos.x; ((float *)S.py)[row] = pos.y; ((float *)S.pz)[row] = pos.z;
-      }
-      __syncthreads();
-      // ---- P1 sweep: one warp per home pair
+      __syncthreads();  // (E) rows and pair tables are ready
+      if (tid < FT_GROUPS) S.grpCount[tid] = 0;  // consumed; clean for the next batch
+      // ---- while the block is swept, warp 0 fetches the next block's cell table
+      if (warp == 0 && b0 == hBeg) ft_fetch_block(d, S.halo[cur ^ 1], cellStart, cellList, nBlocks, cellCursor, lane);
+      // ---- P1 sweep: one warp per home pair, pairs handed out through a shared cursor
       const int totalPairs = S.pairStart[FT_GROUPS];
+      const unsigned laneOff = (unsigned)lane * 4u;
 #pragma unroll 1
-      for (int t = warp; t < totalPairs; t += FT_WARPS) {
+      while (true) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(&S.pairCursor, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= totalPairs) break;
         const int gg = S.pairGroup[t];
         if (S.bad[gg]) continue;
         const int pr = (S.grpStart[gg] >> 1) + (t - S.pairStart[gg]);
         const float2 hx = S.px[pr], hy = S.py[pr], hz = S.pz[pr];
-        const unsigned *wtab = S.word[gg];
+        const unsigned short *wtab = S.wordOff[gg];
         const int nch = S.nWords[gg];
         unsigned keep0 = 0, keep1 = 0;
+        const unsigned char *xb = reinterpret_cast<const unsigned char *>(S.X) + laneOff;
+        const unsigned char *yb = reinterpret_cast<const unsigned char *>(S.Y) + laneOff;
+        const unsigned char *zb = reinterpret_cast<const unsigned char *>(S.Z) + laneOff;
 #pragma unroll 4
         for (int c = 0; c < nch; c++) {
-          const unsigned wd = wtab[c];
-          const int s = (int)(wd & 0xffffu) + lane;
-          const unsigned valid = 0xffffffffu >> (31u - (wd >> 16));
-          const float cx = S.X[s], cy = S.Y[s], cz = S.Z[s];
+          const unsigned off = wtab[c];
+          const float cx = *reinterpret_cast<const float *>(xb + off);
+          const float cy = *reinterpret_cast<const float *>(yb + off);
+          const float cz = *reinterpret_cast<const float *>(zb + off);
           const float2 ncx = make_float2(-cx, -cx), ncy = make_float2(-cy, -cy), ncz = make_float2(-cz, -cz);
           float2 ex = __fadd2_rn(hx, ncx), ey = __fadd2_rn(hy, ncy), ez = __fadd2_rn(hz, ncz);
           float2 dd = __ffma2_rn(ez, ez, __ffma2_rn(ey, ey, __fmul2_rn(ex, ex)));
-          const unsigned m0 = __ballot_sync(0xffffffffu, dd.x <= rfilt2) & valid;
-          const unsigned m1 = __ballot_sync(0xffffffffu, dd.y <= rfilt2) & valid;
+          const unsigned m0 = __ballot_sync(0xffffffffu, dd.x <= rfilt2);
+          const unsigned m1 = __ballot_sync(0xffffffffu, dd.y <= rfilt2);
           if (lane == c) { keep0 = m0; keep1 = m1; }
         }
         if (lane < nch) {
-          S.masks[(2 * pr) * FT_MSTRIDE + lane] = keep0;
-          S.masks[(2 * pr + 1) * FT_MSTRIDE + lane] = keep1;
+          const unsigned valid = S.wordValid[gg][lane];
+          S.masks[(2 * pr) * FT_MSTRIDE + lane] = keep0 & valid;
+          S.masks[(2 * pr + 1) * FT_MSTRIDE + lane] = keep1 & valid;
         }
       }
-      __syncthreads();
+      __syncthreads();  // (F) all mask rows are written
       // ---- P2 select: one thread per home particle
+      if (tid == 0) S.pairCursor = 0;
+      for (int r = tid; r < FT_ROWPAD / 2; r += FT_THREADS) {  // rows back to "no particle" for the next batch
+        S.px[r] = make_float2(FAR, FAR); S.py[r] = make_float2(FAR, FAR); S.pz[r] = make_float2(FAR, FAR);
+      }
       if (tid >= hb) continue;
       if (S.bad[g]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
-      unsigned *mrow = S.masks + row * FT_MSTRIDE;
-      // bit ranges of the 8 cells, in visiting order -> hit list (scan order)
+      const unsigned *mrow = S.masks + row * FT_MSTRIDE;
+      // 30-bin radial histogram in registers: 3 words x 10 bins x 6 bits (a particle keeps <= FT_CAP < 64 hits)
+      unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;
+      // One flat loop: an iteration either opens the next segment or consumes one hit of the current one
+      // (exact distance, hit list in scan order, 30-bin radial histogram of everything within h, :157-161).
       int nh = 0;
-#pragma unroll 1
-      for (int k = 0; k < 8; k++) {
-        const int n = S.cntK[g][k];
-        if (n == 0) continue;
-        const int lo = S.bitLo[g][k], hi = lo + n;  // [lo, hi)
-        const int sOff = S.sB[g][k] - lo;           // bit position + sOff = staged index
-        const int self = id - S.dG[g][k] - sOff;    // bit position of this particle, if it lies in this cell
-        const unsigned tag = (unsigned)k << 12;
-        int c = lo >> 5;
-        const int cLast = (hi - 1) >> 5;
-        unsigned m = mrow[c] & (0xffffffffu << (lo & 31));
+      {
+        const unsigned *segM = S.segMask[g], *segI = S.segInfo[g];
+        const int nSeg = S.nSeg[g];
+        int sg = -1, sbase = 0, dGc = 0;
+        unsigned m = 0u, tag = 0u;
         while (true) {
-          if (c == cLast) m &= 0xffffffffu >> (31 - ((hi - 1) & 31));
-          while (m) {
-            const int bit = (c << 5) + __ffs(m) - 1;
-            m &= m - 1;
-            if (bit != self) {
-              if (nh < FT_CAP) S.hits[nh][tid] = (unsigned short)(tag | (unsigned)(bit + sOff));
-              nh++;
+          if (m == 0u) {
+            if (++sg >= nSeg) break;
+            const unsigned info = segI[sg];
+            m = mrow[info >> 16] & segM[sg];
+            sbase = (int)(info & 0x1fffu) - 32;
+            tag = (info >> 13) & 7u;
+            dGc = S.dG[g][tag];
+            continue;
+          }
+          const int s = sbase + __ffs(m) - 1;
+          m &= m - 1;
+          if (s + dGc == id) continue;  // j == id, :148
+          if (nh < FT_CAP) S.hits[nh][tid] = (unsigned short)((tag << 12) | (unsigned)s);
+          nh++;
+          float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
+          float dd = ex * ex + ey * ey + ez * ez;
+          if (dd <= h2) {
+            // bin (int)(sqrtf(dd)*30/h): approximate guess, made exact with the host-built thresholds
+            float sq;
+            asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
+            int e = (int)(sq * d.binScale);
+            e = min(e, SPH_RADIUS_SEGMENTS);
+            const int b = e + ((dd >= S.binT[e + 1]) ? 1 : 0) - ((dd < S.binT[e]) ? 1 : 0);
+            if (b < SPH_RADIUS_SEGMENTS) {
+              const int w = (b >= 10 ? 1 : 0) + (b >= 20 ? 1 : 0);
+              const unsigned long long inc = 1ull << ((b - 10 * w) * 6);
+              hist0 += (w == 0) ? inc : 0ull;
+              hist1 += (w == 1) ? inc : 0ull;
+              hist2 += (w == 2) ? inc : 0ull;
             }
           }
-          if (c == cLast) break;
-          m = mrow[++c];
         }
       }
       if (nh > FT_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
-#pragma unroll
-      for (int b = 0; b < SPH_RADIUS_SEGMENTS; b++) S.hist[b][tid] = 0;
-      // exact distances + 30-bin radial histogram of everything within h (:157-161)
-      for (int t = 0; t < nh; t++) {
-        const int s = S.hits[t][tid] & 0xfff;
-        float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
-        float dd = ex * ex + ey * ey + ez * ez;
-        if (dd <= h2) {
-          // bin (int)(sqrtf(dd)*30/h): approximate guess, made exact with the host-built thresholds
-          float sq;
-          asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
-          int e = (int)(sq * d.binScale);
-          e = min(e, SPH_RADIUS_SEGMENTS);
-          const int b = e + ((dd >= S.binT[e + 1]) ? 1 : 0) - ((dd < S.binT[e]) ? 1 : 0);
-          if (b < SPH_RADIUS_SEGMENTS) {
-            unsigned hv = S.hist[b][tid];
-            if (hv < 255u) S.hist[b][tid] = (unsigned char)(hv + 1u);  // saturation keeps the >32 logic exact
-          }
-        }
-      }
       // radius threshold (:310-324)
-      int j = 0, sum = 0;
-      while (j < SPH_RADIUS_SEGMENTS) {
-        sum += S.hist[j][tid];
-        if (sum == SPH_NB) break;
-        if (sum > SPH_NB) { j--; break; }
-        j++;
+      int j = SPH_RADIUS_SEGMENTS;
+      {
+        int sum = 0;
+        bool open = true;
+#pragma unroll
+        for (int jj = 0; jj < SPH_RADIUS_SEGMENTS; jj++) {
+          const unsigned long long hw = jj < 10 ? hist0 : (jj < 20 ? hist1 : hist2);
+          sum += (int)((hw >> ((jj % 10) * 6)) & 63ull);
+          if (open && sum >= SPH_NB) { j = (sum == SPH_NB) ? jj : jj - 1; open = false; }
+        }
       }
       const float r_thr = (float)(j + 1) * d.h / SPH_RADIUS_SEGMENTS;
       const float r2 = r_thr * r_thr;
@@ -434,7 +512,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
         float dd = ex * ex + ey * ey + ez * ez;
         if (dd <= r2) {
-          mrow[found] = (unsigned)(s + S.dG[g][hv >> 12]);  // own row: its masks are consumed
+          S.hits[found][tid] = (unsigned short)hv;  // in-place compaction: found <= t
           if (WITH_DENSITY) {
             float r = sqrtf(dd) * d.simScale;
             float rr = r * r;
@@ -444,13 +522,17 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         }
       }
 #pragma unroll 8
-      for (int q = 0; q < SPH_NB; q++) nb[nb_index(id, q)] = (q < found) ? (int)mrow[q] : SPH_NO_ID;
+      for (int q = 0; q < SPH_NB; q++) {
+        const unsigned hv = S.hits[q][tid];
+        nb[nb_index(id, q)] = (q < found) ? (int)(hv & 0xfffu) + S.dG[g][hv >> 12] : SPH_NO_ID;
+      }
       if (WITH_DENSITY) {
         if (density < (double)d.hScaled6) density = (double)d.hScaled6;
         density *= d.massWpoly6;
         rho[id] = (float)density;
       }
     }
+    cur ^= 1;
   }
 }
 

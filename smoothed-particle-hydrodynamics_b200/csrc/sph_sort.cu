@@ -154,7 +154,9 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
   unsigned rank = 0;
   for (unsigned t = b; t < e; ++t) rank += (tmpSerial[t] < serial) ? 1u : 0u;
   unsigned dst = b + rank;
-  if (rank == 0) cellList[atomicAdd(cellListCount, 1u)] = bin;  // one entry per non-empty cell
+  // work list of the neighbour search: one entry per HOME BLOCK (cells 2b, 2b+1), posted by the first
+  // particle of the block's first non-empty cell
+  if (rank == 0 && ((bin & 1u) == 0u || cellStart[bin - 1] == b)) cellList[atomicAdd(cellListCount, 1u)] = bin;
   particleIndex[dst] = make_uint2(cell, serial);
   if (REORDER) {  // sortPostPass, sphFluid.cl:457-465
     float4 p = position[serial];
