@@ -137,9 +137,9 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 //   group   sorts the home particles by (home cell, octant): all particles of a cell that sit in the
 //           same octant of it visit the same 8 cells in the same order (sphFluid.cl:248-308). Those 8
 //           cells are 4 RUNS of two id-adjacent cells, and a run is contiguous in the staging area;
-//   sweep   (P1) one warp per PAIR of home particles of a group: the pair's coordinates live in
-//           registers as fp32x2 operands, lanes hold 32 consecutive staged candidates of a run, both
-//           squared distances come out of Blackwell's packed fp32x2 pipe, two ballots give the
+//   sweep   (P1) one warp per QUAD of home particles of a group: the quad's coordinates live in
+//           registers as two sets of fp32x2 operands, lanes hold 32 consecutive staged candidates of a run, the four
+//           squared distances come out of Blackwell's packed fp32x2 pipe, four ballots give the
 //           32-bit hit masks of the chunk, lane w keeps mask word w, and the row of words goes to
 //           shared memory. The test is a conservative FILTER (radius 31h/30 — the largest r_thr the
 //           reference can choose — slightly inflated, FMA allowed): nothing inexact reaches the output;
@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #define FT_WARPS (FT_THREADS / 32)
 #define FT_ROWS FT_THREADS        // home particles per batch (thread t of P2 owns particle b0 + t)
 #define FT_GROUPS 16              // (home cell 0/1) x octant
-#define FT_ROWPAD (FT_ROWS + FT_GROUPS)  // rows in group order, every group padded to an even size
+#define FT_ROWPAD (FT_ROWS + 3 * FT_GROUPS)  // rows in group order, every group padded to a multiple of 4
 #define FT_NCELL 36               // staged cells: id offset hx in [-1,2], y-row and z-slab offsets in [-1,1]
 #define FT_CMAX 2560              // staged candidates (36 cells x 71); staged indices fit 12 bits
 #define FT_NCH 24                 // mask words per row (<= 32: lane w of the sweeping warp keeps word w)
@@ -173,19 +173,21 @@ struct FtHalo {                   // cell table of one home block
 
 struct FtShared {
   float X[FT_CMAX + 32], Y[FT_CMAX + 32], Z[FT_CMAX + 32];  // +32: a run's last chunk may read past its end
-  unsigned masks[FT_ROWPAD * FT_MSTRIDE];
+  unsigned masks[FT_THREADS * FT_MSTRIDE];   // mask row of P2 thread t (particle b0 + t)
   unsigned short hits[FT_CAP][FT_THREADS];   // (k << 12) | staged index, scan order
-  float2 px[FT_ROWPAD / 2], py[FT_ROWPAD / 2], pz[FT_ROWPAD / 2];
+  __align__(16) float px[FT_ROWPAD], py[FT_ROWPAD], pz[FT_ROWPAD];  // home coordinates, row order (FAR = no particle)
+  __align__(4) unsigned char rowTid[FT_ROWPAD];                     // row -> owning P2 thread (255 = none)
   unsigned short wordOff[FT_GROUPS][FT_NCH];  // mask word w of a group: byte offset of its bit-0 candidate in X/Y/Z
   unsigned wordValid[FT_GROUPS][FT_NCH]; // ... and which of its 32 bits are real candidates
   unsigned segMask[FT_GROUPS][FT_NSEG];  // segment: bits of mask word (info >> 16) that belong to cell k
   unsigned segInfo[FT_GROUPS][FT_NSEG];  // (staged index of bit 0 + 32) | k << 13 | word << 16
   int dG[FT_GROUPS][8];                  // staged index + dG = sorted particle id, per visited cell k
   int nWords[FT_GROUPS], nSeg[FT_GROUPS], bad[FT_GROUPS];
+  int bitLo0[FT_GROUPS];                 // row bit of the first particle of the group's own cell (k = 0)
   float binT[SPH_RADIUS_SEGMENTS + 2];
   FtHalo halo[2];
-  int grpCount[FT_GROUPS], grpStart[FT_GROUPS], pairStart[FT_GROUPS + 1];
-  unsigned char pairGroup[FT_ROWPAD / 2];
+  int grpCount[FT_GROUPS], quadStart[FT_GROUPS + 1];
+  unsigned char quadGroup[FT_ROWPAD / 4];
   int pairCursor;
 };
 
@@ -293,8 +295,9 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
   if (tid < 32) { S.X[FT_CMAX + tid] = FAR; S.Y[FT_CMAX + tid] = FAR; S.Z[FT_CMAX + tid] = FAR; }
   if (tid < FT_GROUPS) S.grpCount[tid] = 0;
   if (tid == 0) S.pairCursor = 0;
-  for (int r = tid; r < FT_ROWPAD / 2; r += FT_THREADS) {
-    S.px[r] = make_float2(FAR, FAR); S.py[r] = make_float2(FAR, FAR); S.pz[r] = make_float2(FAR, FAR);
+  for (int r = tid; r < FT_ROWPAD; r += FT_THREADS) {
+    S.px[r] = FAR; S.py[r] = FAR; S.pz[r] = FAR;
+    S.rowTid[r] = 255;
   }
   if (warp == 0) ft_fetch_block(d, S.halo[0], cellStart, cellList, nBlocks, cellCursor, lane);
   int cur = 0;
@@ -334,6 +337,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
       q.cell(k, H, t, lo);
       const int n = H.cnt[t], hi = lo + n;
       S.dG[g][k] = H.gStart[t] - H.sStart[t];
+      if (k == 0) S.bitLo0[g] = lo;
       if (n) {
         for (int w = lo >> 5; w <= (hi - 1) >> 5; w++, sg++) {
           const int a = max(lo, w * 32) - w * 32, b = min(hi, w * 32 + 32) - w * 32;  // bits [a, b) of word w
@@ -376,119 +380,131 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         rankInG = atomicAdd(&S.grpCount[g], 1);
       }
       __syncthreads();  // (C) group sizes are final; tables and staging are visible
-      int row = 0;
-      {
+      if (tid < hb) {   // rows in group order, every group padded to a multiple of 4 (one QUAD = one sweep)
         int gs = 0;
 #pragma unroll
-        for (int q = 0; q < FT_GROUPS; q++) gs += (q < g) ? ((S.grpCount[q] + 1) & ~1) : 0;
-        row = gs + rankInG;
+        for (int q = 0; q < FT_GROUPS; q++) gs += (q < g) ? ((S.grpCount[q] + 3) & ~3) : 0;
+        const int row = gs + rankInG;
+        S.px[row] = pos.x; S.py[row] = pos.y; S.pz[row] = pos.z;
+        S.rowTid[row] = (unsigned char)tid;
       }
-      if (tid < hb) { ((float *)S.px)[row] = pos.x; ((float *)S.py)[row] = pos.y; ((float *)S.pz)[row] = pos.z; }
       if (tid < FT_GROUPS) {
-        int ps = 0;
-        for (int q = 0; q < tid; q++) ps += (S.grpCount[q] + 1) >> 1;
-        const int np = (S.grpCount[tid] + 1) >> 1;
-        S.grpStart[tid] = 2 * ps;
-        S.pairStart[tid] = ps;
-        if (tid == FT_GROUPS - 1) S.pairStart[FT_GROUPS] = ps + np;
-        for (int q = 0; q < np; q++) S.pairGroup[ps + q] = (unsigned char)tid;
+        int qs = 0;
+        for (int q = 0; q < tid; q++) qs += (S.grpCount[q] + 3) >> 2;
+        const int nq = (S.grpCount[tid] + 3) >> 2;
+        S.quadStart[tid] = qs;
+        if (tid == FT_GROUPS - 1) S.quadStart[FT_GROUPS] = qs + nq;
+        for (int q = 0; q < nq; q++) S.quadGroup[qs + q] = (unsigned char)tid;
       }
-      __syncthreads();  // (E) rows and pair tables are ready
+      __syncthreads();  // (E) rows and quad tables are ready
       if (tid < FT_GROUPS) S.grpCount[tid] = 0;  // consumed; clean for the next batch
       // ---- while the block is swept, warp 0 fetches the next block's cell table
       if (warp == 0 && b0 == hBeg) ft_fetch_block(d, S.halo[cur ^ 1], cellStart, cellList, nBlocks, cellCursor, lane);
-      // ---- P1 sweep: one warp per home pair, pairs handed out through a shared cursor
-      const int totalPairs = S.pairStart[FT_GROUPS];
-      const unsigned laneOff = (unsigned)lane * 4u;
+      // ---- P1 sweep: one warp per quad of home particles, quads handed out through a shared cursor
+      const int totalQuads = S.quadStart[FT_GROUPS];
+      const unsigned char *xb = reinterpret_cast<const unsigned char *>(S.X) + lane * 4;
+      const unsigned char *yb = reinterpret_cast<const unsigned char *>(S.Y) + lane * 4;
+      const unsigned char *zb = reinterpret_cast<const unsigned char *>(S.Z) + lane * 4;
 #pragma unroll 1
       while (true) {
         int t = 0;
         if (lane == 0) t = atomicAdd(&S.pairCursor, 1);
         t = __shfl_sync(0xffffffffu, t, 0);
-        if (t >= totalPairs) break;
-        const int gg = S.pairGroup[t];
+        if (t >= totalQuads) break;
+        const int gg = S.quadGroup[t];
         if (S.bad[gg]) continue;
-        const int pr = (S.grpStart[gg] >> 1) + (t - S.pairStart[gg]);
-        const float2 hx = S.px[pr], hy = S.py[pr], hz = S.pz[pr];
+        const float2 hxa = reinterpret_cast<const float2 *>(S.px)[2 * t], hxb = reinterpret_cast<const float2 *>(S.px)[2 * t + 1];
+        const float2 hya = reinterpret_cast<const float2 *>(S.py)[2 * t], hyb = reinterpret_cast<const float2 *>(S.py)[2 * t + 1];
+        const float2 hza = reinterpret_cast<const float2 *>(S.pz)[2 * t], hzb = reinterpret_cast<const float2 *>(S.pz)[2 * t + 1];
         const unsigned short *wtab = S.wordOff[gg];
         const int nch = S.nWords[gg];
-        unsigned keep0 = 0, keep1 = 0;
-        const unsigned char *xb = reinterpret_cast<const unsigned char *>(S.X) + laneOff;
-        const unsigned char *yb = reinterpret_cast<const unsigned char *>(S.Y) + laneOff;
-        const unsigned char *zb = reinterpret_cast<const unsigned char *>(S.Z) + laneOff;
-#pragma unroll 4
+        unsigned keep0 = 0, keep1 = 0, keep2 = 0, keep3 = 0;
+#pragma unroll 2
         for (int c = 0; c < nch; c++) {
           const unsigned off = wtab[c];
           const float cx = *reinterpret_cast<const float *>(xb + off);
           const float cy = *reinterpret_cast<const float *>(yb + off);
           const float cz = *reinterpret_cast<const float *>(zb + off);
           const float2 ncx = make_float2(-cx, -cx), ncy = make_float2(-cy, -cy), ncz = make_float2(-cz, -cz);
-          float2 ex = __fadd2_rn(hx, ncx), ey = __fadd2_rn(hy, ncy), ez = __fadd2_rn(hz, ncz);
-          float2 dd = __ffma2_rn(ez, ez, __ffma2_rn(ey, ey, __fmul2_rn(ex, ex)));
-          const unsigned m0 = __ballot_sync(0xffffffffu, dd.x <= rfilt2);
-          const unsigned m1 = __ballot_sync(0xffffffffu, dd.y <= rfilt2);
-          if (lane == c) { keep0 = m0; keep1 = m1; }
+          const float2 exa = __fadd2_rn(hxa, ncx), eya = __fadd2_rn(hya, ncy), eza = __fadd2_rn(hza, ncz);
+          const float2 exb = __fadd2_rn(hxb, ncx), eyb = __fadd2_rn(hyb, ncy), ezb = __fadd2_rn(hzb, ncz);
+          const float2 da = __ffma2_rn(eza, eza, __ffma2_rn(eya, eya, __fmul2_rn(exa, exa)));
+          const float2 db = __ffma2_rn(ezb, ezb, __ffma2_rn(eyb, eyb, __fmul2_rn(exb, exb)));
+          const unsigned m0 = __ballot_sync(0xffffffffu, da.x <= rfilt2);
+          const unsigned m1 = __ballot_sync(0xffffffffu, da.y <= rfilt2);
+          const unsigned m2 = __ballot_sync(0xffffffffu, db.x <= rfilt2);
+          const unsigned m3 = __ballot_sync(0xffffffffu, db.y <= rfilt2);
+          if (lane == c) { keep0 = m0; keep1 = m1; keep2 = m2; keep3 = m3; }
         }
-        if (lane < nch) {
+        if (lane < nch) {  // mask rows are indexed by the owning P2 thread; padding rows have none
           const unsigned valid = S.wordValid[gg][lane];
-          S.masks[(2 * pr) * FT_MSTRIDE + lane] = keep0 & valid;
-          S.masks[(2 * pr + 1) * FT_MSTRIDE + lane] = keep1 & valid;
+          const uchar4 own = reinterpret_cast<const uchar4 *>(S.rowTid)[t];
+          if (own.x != 255) S.masks[own.x * FT_MSTRIDE + lane] = keep0 & valid;
+          if (own.y != 255) S.masks[own.y * FT_MSTRIDE + lane] = keep1 & valid;
+          if (own.z != 255) S.masks[own.z * FT_MSTRIDE + lane] = keep2 & valid;
+          if (own.w != 255) S.masks[own.w * FT_MSTRIDE + lane] = keep3 & valid;
         }
       }
       __syncthreads();  // (F) all mask rows are written
       // ---- P2 select: one thread per home particle
       if (tid == 0) S.pairCursor = 0;
-      for (int r = tid; r < FT_ROWPAD / 2; r += FT_THREADS) {  // rows back to "no particle" for the next batch
-        S.px[r] = make_float2(FAR, FAR); S.py[r] = make_float2(FAR, FAR); S.pz[r] = make_float2(FAR, FAR);
+      for (int r = tid; r < FT_ROWPAD; r += FT_THREADS) {  // rows back to "no particle" for the next batch
+        S.px[r] = FAR; S.py[r] = FAR; S.pz[r] = FAR;
+        S.rowTid[r] = 255;
       }
       if (tid >= hb) continue;
       if (S.bad[g]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
-      const unsigned *mrow = S.masks + row * FT_MSTRIDE;
-      // 30-bin radial histogram in registers: 3 words x 10 bins x 6 bits (a particle keeps <= FT_CAP < 64 hits)
-      unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;
-      // One flat loop: an iteration either opens the next segment or consumes one hit of the current one
-      // (exact distance, hit list in scan order, 30-bin radial histogram of everything within h, :157-161).
+      unsigned *mrow = S.masks + tid * FT_MSTRIDE;
+      {  // j == id (:148): the particle's own bit sits in its own cell, the first one visited
+        const int selfBit = S.bitLo0[g] + id - ((g & 8) ? hMid : hBeg);
+        mrow[selfBit >> 5] &= ~(1u << (selfBit & 31));
+      }
+      // walk the row through the segment table -> hit list in scan order. One flat loop: an iteration
+      // either opens the next segment or takes one hit of the current one.
       int nh = 0;
       {
         const unsigned *segM = S.segMask[g], *segI = S.segInfo[g];
         const int nSeg = S.nSeg[g];
-        int sg = -1, sbase = 0, dGc = 0;
-        unsigned m = 0u, tag = 0u;
+        int sg = -1;
+        unsigned m = 0u, hbase = 0u;
         while (true) {
           if (m == 0u) {
             if (++sg >= nSeg) break;
             const unsigned info = segI[sg];
             m = mrow[info >> 16] & segM[sg];
-            sbase = (int)(info & 0x1fffu) - 32;
-            tag = (info >> 13) & 7u;
-            dGc = S.dG[g][tag];
+            hbase = (((info >> 13) & 7u) << 12) + (info & 0x1fffu) - 32u;  // (k << 12) | staged index of bit 0
             continue;
           }
-          const int s = sbase + __ffs(m) - 1;
+          const unsigned hv = hbase + (unsigned)__ffs(m) - 1u;
           m &= m - 1;
-          if (s + dGc == id) continue;  // j == id, :148
-          if (nh < FT_CAP) S.hits[nh][tid] = (unsigned short)((tag << 12) | (unsigned)s);
+          if (nh < FT_CAP) S.hits[nh][tid] = (unsigned short)hv;
           nh++;
-          float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
-          float dd = ex * ex + ey * ey + ez * ez;
-          if (dd <= h2) {
-            // bin (int)(sqrtf(dd)*30/h): approximate guess, made exact with the host-built thresholds
-            float sq;
-            asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
-            int e = (int)(sq * d.binScale);
-            e = min(e, SPH_RADIUS_SEGMENTS);
-            const int b = e + ((dd >= S.binT[e + 1]) ? 1 : 0) - ((dd < S.binT[e]) ? 1 : 0);
-            if (b < SPH_RADIUS_SEGMENTS) {
-              const int w = (b >= 10 ? 1 : 0) + (b >= 20 ? 1 : 0);
-              const unsigned long long inc = 1ull << ((b - 10 * w) * 6);
-              hist0 += (w == 0) ? inc : 0ull;
-              hist1 += (w == 1) ? inc : 0ull;
-              hist2 += (w == 2) ? inc : 0ull;
-            }
-          }
         }
       }
       if (nh > FT_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
+      // exact distances + 30-bin radial histogram of everything within h (:157-161), in registers:
+      // 3 words x 10 bins x 6 bits (a particle keeps <= FT_CAP < 64 hits)
+      unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;
+      for (int t = 0; t < nh; t++) {
+        const int s = S.hits[t][tid] & 0xfff;
+        float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
+        float dd = ex * ex + ey * ey + ez * ez;
+        if (dd <= h2) {
+          // bin (int)(sqrtf(dd)*30/h): approximate guess, made exact with the host-built thresholds
+          float sq;
+          asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
+          int e = (int)(sq * d.binScale);
+          e = min(e, SPH_RADIUS_SEGMENTS);
+          const int b = e + ((dd >= S.binT[e + 1]) ? 1 : 0) - ((dd < S.binT[e]) ? 1 : 0);
+          if (b < SPH_RADIUS_SEGMENTS) {
+            const int w = (b >= 10 ? 1 : 0) + (b >= 20 ? 1 : 0);
+            const unsigned long long inc = 1ull << ((b - 10 * w) * 6);
+            hist0 += (w == 0) ? inc : 0ull;
+            hist1 += (w == 1) ? inc : 0ull;
+            hist2 += (w == 2) ? inc : 0ull;
+          }
+        }
+      }
       // radius threshold (:310-324)
       int j = SPH_RADIUS_SEGMENTS;
       {
@@ -574,7 +590,8 @@ static void launch_tiles(sph_ctx *c) {
 }
 
 void launch_find_neighbors(sph_ctx *c, bool with_density) {
-  if (c->force_generic_neighbors) {
+  // the tiled kernel assumes the 36 cells around a home block are distinct: true for grids >= 4 x 3 x 3
+  if (c->force_generic_neighbors || c->d.gx < 4 || c->d.gy < 3 || c->d.gz < 3) {
     int blocks = (c->d.N + 127) / 128;
     if (with_density)
       k_find_neighbors_generic<true><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho);
