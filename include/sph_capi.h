@@ -200,6 +200,45 @@ long long sph_launch_count(const sph_ctx *ctx);
 void *sph_host_alloc(size_t bytes);
 void sph_host_free(void *p);
 
+/* ---- multi-device slab extension (CUDA library only). The reference is single-device
+ * (owOpenCLSolver.cpp:157-182); SURVEY.md 8e / DESIGN.md 7 define this protocol. One context per rank;
+ * the rank owns hash-cell z-layers [z0, z1) and keeps ghost copies of layers z0-1 and z1. The library
+ * classifies, packs and unpacks on the device; the caller moves the bytes between ranks
+ * (smoothed-particle-hydrodynamics_b200/slab.py: torch.distributed / NCCL). side: 0 = down (z0-1), 1 = up (z1). ---- */
+
+/* Bytes of one particle record (position, velocity, global id) in migration / ghost buffers. */
+int sph_slab_record_bytes(void);
+/* Make a context created with particle_count = CAPACITY a slab rank; its first n_owned particles are owned,
+ * gid[] are their global ids (= original indices of the single-device run). Needs hash_mask 0xffffffff. */
+int sph_slab_begin(sph_ctx *ctx, int n_owned, const uint32_t *gid, int z0, int z1, int has_down, int has_up,
+                   int mig_cap, int halo_cap);
+/* Phase 1 of a step: owned particles -> keep / migrate down / migrate up, plus copies of the kept boundary
+ * layers. The four DEVICE buffers hold mig_cap / halo_cap records. counts = {mig_down, ghost_down, mig_up,
+ * ghost_up}. Synchronous (the counts size the transfers). */
+int sph_slab_classify(sph_ctx *ctx, void *mig_down, void *ghost_down, void *mig_up, void *ghost_up, int counts[4]);
+/* Phase 2: the four received DEVICE buffers and their record counts {mig_from_down, ghost_from_down,
+ * mig_from_up, ghost_from_up}; rebuilds the local particle set (owned + ghosts). Asynchronous. */
+int sph_slab_absorb(sph_ctx *ctx, const void *mig_from_down, const void *ghost_from_down, const void *mig_from_up,
+                    const void *ghost_from_up, const int incoming[4]);
+/* out = {n_owned, n_local, n_send_down, n_send_up, n_recv_down, n_recv_up} (halo element counts). */
+int sph_slab_info(const sph_ctx *ctx, int out[6]);
+/* Halo refresh of field 0 = rho(t) (4 B), 1 = (pressure, rho*) (8 B), 2 = predicted position (16 B): gather the
+ * values a neighbour's ghosts need into a DEVICE buffer / scatter a received buffer into the local ghosts. */
+int sph_slab_pack(sph_ctx *ctx, int field, int side, void *buf);
+int sph_slab_unpack(sph_ctx *ctx, int field, int side, const void *buf);
+/* Owned particles (any order) and their global ids, to host memory. Synchronous. */
+int sph_slab_read_owned(sph_ctx *ctx, float *pos4, float *vel4, uint32_t *gid);
+const char *sph_slab_last_error(void);
+/* The fused step in the five pieces between which a slab rank refreshes its ghosts:
+ * 0 | rho | 1 | (p,rho*) | 2 | x* | 3 | (p,rho*) | 2 | x* | 3 | (p,rho*) | 4   for max_iteration = 3. */
+int sph_step_part(sph_ctx *ctx, int part);
+/* Run the context on a caller-owned CUDA stream (cudaStream_t), NULL = its own stream again. */
+int sph_set_stream(sph_ctx *ctx, void *cuda_stream);
+/* Raw device memory for exchange buffers; synchronous copy between any host / device pointers. */
+void *sph_device_alloc(size_t bytes);
+void sph_device_free(void *p);
+int sph_device_copy(void *dst, const void *src, size_t bytes);
+
 #ifdef __cplusplus
 }
 #endif

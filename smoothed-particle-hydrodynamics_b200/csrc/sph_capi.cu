@@ -158,6 +158,7 @@ void sph_destroy(sph_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  slab_destroy(c);
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
@@ -165,7 +166,7 @@ void sph_destroy(sph_ctx *c) {
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
-  if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->ownStream) cudaStreamDestroy(c->ownStream);
   delete c;
 }
 
@@ -206,6 +207,7 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   bool ok = true;
 #define A(x) ok = ok && ((e = (x)) == cudaSuccess)
   A(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->ownStream = c->stream;
   A(dalloc(&c->position, 2 * N));
   A(dalloc(&c->velocity, 2 * N));
   A(dalloc(&c->particleIndex, N));
@@ -348,6 +350,62 @@ int sph_step(sph_ctx *c) {
   { ProfScope s(c, PK_MEMBRANES); launch_membrane_interaction(c, true); }
   c->launches += 8 + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
   return check_launch(c, false);
+}
+
+// ---- multi-device slab extension: the fused step in the pieces between which a slab rank refreshes its
+// ghosts (sph_slab.cu). part 0: hash, sort, neighbour search + rho(t)            -> refresh rho
+//                       part 1: forces (+ predict #0), predictDensity + correct  -> refresh (p, rho*)
+//                       part 2: pressure force + predict next                    -> refresh x*
+//                       part 3: predictDensity + correctPressure                 -> refresh (p, rho*)
+//                       part 4: pressure force + integrate, membranes
+// A step with max_iteration = 3 is 0 | 1 | 2 | 3 | 2 | 3 | 4. Same kernels, same order as sph_step.
+int sph_step_part(sph_ctx *c, int part) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  CU(cudaSetDevice(c->device));
+  switch (part) {
+    case 0:
+      { ProfScope s(c, PK_HASH); launch_hash_count(c, false); }
+      { ProfScope s(c, PK_SORT); launch_sort(c, true); }
+      { ProfScope s(c, PK_NEIGHBORS); launch_find_neighbors(c, true); }
+      c->launches += 5;
+      break;
+    case 1:
+      { ProfScope s(c, PK_FORCES); launch_forces(c, true); }
+      if (c->d.numElastic > 0 && c->has_elastic) { ProfScope s(c, PK_ELASTIC); launch_elastic(c); c->launches++; }
+      { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); }
+      c->launches += 2;
+      break;
+    case 2: { ProfScope s(c, PK_PRESSURE_FORCE); launch_pressure_force(c, 1); } c->launches++; break;
+    case 3: { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); } c->launches++; break;
+    case 4:
+      { ProfScope s(c, PK_PRESSURE_FORCE_INTEGRATE); launch_pressure_force(c, 2); }
+      { ProfScope s(c, PK_MEMBRANES); launch_membrane_interaction(c, true); }
+      c->launches += 2;
+      break;
+    default: return fail(SPH_E_INVALID, "sph_step_part: unknown part");
+  }
+  return check_launch(c, false);
+}
+
+// Run the context's work on a caller-owned CUDA stream (e.g. torch's current stream, so that collectives
+// issued by the caller are ordered with the kernels); NULL restores the context's own stream.
+int sph_set_stream(sph_ctx *c, void *cuda_stream) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->ownStream;
+  return 0;
+}
+
+void *sph_device_alloc(size_t bytes) {
+  void *p = nullptr;
+  return cudaMalloc(&p, bytes ? bytes : 1) == cudaSuccess ? p : nullptr;
+}
+void sph_device_free(void *p) { if (p) cudaFree(p); }
+// synchronous copy between any two of {host, device} buffers (unified addressing picks the direction)
+int sph_device_copy(void *dst, const void *src, size_t bytes) {
+  CU(cudaMemcpy(dst, src, bytes, cudaMemcpyDefault));
+  return 0;
 }
 
 // ---- instrumentation (not part of the reference interface; used by bench.py / the C++ facade) ----

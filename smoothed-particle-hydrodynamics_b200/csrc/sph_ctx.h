@@ -3,6 +3,8 @@
 #pragma once
 #include "sph_device.cuh"
 
+struct SlabState;
+
 struct sph_ctx {
   sph_params p;
   DevParams d;
@@ -46,6 +48,9 @@ struct sph_ctx {
   bool has_elastic, has_membranes, has_pml;
   bool neighbors_valid;
   void *profiler;              // Profiler* when per-kernel event timing is on
+  SlabState *slab;             // non-null: this context is one slab rank of a multi-device fluid (sph_slab.cu)
+  unsigned *rankKey;           // in-cell ranking key per original index (global ids of a slab rank); null = the index itself
+  cudaStream_t ownStream;      // the stream created with the context (c->stream may be replaced by sph_set_stream)
   long long launches;          // kernels launched by sph_step so far
 };
 
@@ -67,6 +72,8 @@ void launch_predict_density(sph_ctx *c, bool fuse_correct);
 void launch_correct_pressure(sph_ctx *c);
 void launch_pressure_force(sph_ctx *c, int mode);  // 0 = force only, 1 = + predictPositions, 2 = + integrate
 void launch_integrate(sph_ctx *c);
+// sph_slab.cu
+void slab_destroy(sph_ctx *c);
 // sph_membranes.cu
 void launch_clear_membrane_buffers(sph_ctx *c);
 void launch_membrane_interaction(sph_ctx *c, bool fuse_finalize);

@@ -144,7 +144,8 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
                                                       float4 *__restrict__ sortedPosition,
                                                       float4 *__restrict__ sortedVelocity,
                                                       float *__restrict__ sortedType, float4 *__restrict__ spT, unsigned *__restrict__ cellList,
-                                                      unsigned *__restrict__ cellListCount) {
+                                                      unsigned *__restrict__ cellListCount,
+                                                      const unsigned *__restrict__ rankKey) {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= d.N) return;
   unsigned serial = tmpSerial[s];
@@ -152,7 +153,14 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
   unsigned bin = cell < (unsigned)d.G ? cell : (unsigned)d.G - 1u;
   unsigned b = cellStart[bin], e = cellStart[bin + 1];
   unsigned rank = 0;
-  for (unsigned t = b; t < e; ++t) rank += (tmpSerial[t] < serial) ? 1u : 0u;
+  // order within a cell = ascending original index (glibc's stable merge sort in _runSort); a slab rank
+  // ranks by GLOBAL id instead, which is the original index of the single-device run
+  if (rankKey) {
+    const unsigned mine = rankKey[serial];
+    for (unsigned t = b; t < e; ++t) rank += (rankKey[tmpSerial[t]] < mine) ? 1u : 0u;
+  } else {
+    for (unsigned t = b; t < e; ++t) rank += (tmpSerial[t] < serial) ? 1u : 0u;
+  }
   unsigned dst = b + rank;
   // work list of the neighbour search: one entry per HOME BLOCK (cells 2b, 2b+1), posted by the first
   // particle of the block's first non-empty cell
@@ -220,12 +228,12 @@ void launch_sort(sph_ctx *c, bool fuse_reorder) {
     k_rank_reorder<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                    c->particleIndex, c->particleIndexBack, c->position,
                                                                    c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount);
+                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey);
   else
     k_rank_reorder<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                     c->particleIndex, c->particleIndexBack, c->position,
                                                                     c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount);
+                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey);
 }
 
 void launch_reorder(sph_ctx *c) {
