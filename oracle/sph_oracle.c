@@ -801,7 +801,11 @@ int sph_read(sph_ctx *c, int id, void *dst, size_t bytes) {
 
 int sph_write(sph_ctx *c, int id, const void *src, size_t bytes) {
   if (!c || !src) return fail(SPH_E_INVALID, "sph_write: null");
-  if (id != SPH_BUF_POSITION && id != SPH_BUF_VELOCITY) return fail(SPH_E_UNSUPPORTED, "sph_write: buffer not writable");
+  /* POSITION / VELOCITY as the ABI promises; the oracle (test infrastructure) also lets a test overwrite the three
+   * per-stage fields a slab rank refreshes in its ghosts (tests/slab_oracle.py): rho, pressure, sortedPosition. */
+  if (id != SPH_BUF_POSITION && id != SPH_BUF_VELOCITY && id != SPH_BUF_RHO && id != SPH_BUF_PRESSURE &&
+      id != SPH_BUF_SORTED_POSITION)
+    return fail(SPH_E_UNSUPPORTED, "sph_write: buffer not writable");
   size_t have = 0;
   void *dst = buf_ptr(c, id, &have);
   if (bytes > have) return fail(SPH_E_SIZE, "sph_write: too many bytes");
