@@ -105,7 +105,7 @@ def test_error_paths(O):
     with pytest.raises(capi.SphError):
         ctx.stage(99)
     with pytest.raises(capi.SphError):
-        ctx.write("rho", np.zeros(4, np.float32))
+        ctx.write("acceleration", np.zeros((1, 4), np.float32))
     bad = O.default_params()
     with pytest.raises(capi.SphError):
         O.create(bad, np.zeros((0, 4), np.float32), np.zeros((0, 4), np.float32))
