@@ -156,6 +156,68 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def run_slab_rank(args, rank, world, local, torch, dist, L, warmup, steps):
+    """N > 1: ONE fluid, slab-decomposed along z over the ranks: ghost layers, per-stage halo
+    refresh and migration over torch.distributed point-to-point (NCCL / NVLink). Weak scaling: every rank owns
+    the named workload's particle count. Returns (ms, e2e_ms, n_owned, profile, launches, info)."""
+    slab = importlib.import_module(PKG + ".slab")
+    sc = scenes.slab_scene(args.workload, world, rank)
+    p = L.default_params(box=sc["box"])
+    p.hash_mask = 0xFFFFFFFF
+    p.particle_count = len(sc["gid"])
+    p.num_liquid = sc["n_liquid"]
+    p.num_boundary = len(sc["gid"]) - sc["n_liquid"]
+    dev = torch.device("cuda", local)
+    # the library's kernels and torch's NCCL transfers must be ordered on ONE stream: a side stream of torch's
+    # (a non-zero handle; the context's own stream is non-blocking and would not order with the legacy stream 0)
+    side = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(side):
+        r = slab.SlabRank(L, p, sc["position"], sc["velocity"], sc["gid"], sc["z0"], sc["z1"], rank, world, device=local,
+                          alloc=slab.DistTransport.allocator(dev), halo_cap=sc["halo_cap"], mig_cap=sc["mig_cap"])
+        r.set_stream(torch.cuda.current_stream().cuda_stream)  # kernels and NCCL transfers ordered on one stream
+        tr = slab.DistTransport(r, dev)
+        for _ in range(warmup):
+            slab.slab_step(tr)
+        r.ctx.profile(True)
+        dist.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = r.ctx.launch_count()
+        a.record()
+        for _ in range(steps):
+            slab.slab_step(tr)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b)
+        launches = r.ctx.launch_count() - l0 + steps * (4 + 14)  # + classify/append/iota and the pack/unpack kernels
+        prof = r.ctx.profile_report()
+        r.ctx.profile(False)
+        dist.barrier()
+        # e2e: muscle signal up, step, owned positions back to pinned host memory, every step
+        cap = r.capacity
+        host_pos = L.pinned_array((cap, 4))
+        host_sig = L.pinned_array((100,))
+        e2e_steps = max(3, min(steps, 10))
+        import ctypes as C
+        def one(s):
+            host_sig[:] = muscle_signal(s)
+            r.ctx.set_muscles(host_sig)
+            slab.slab_step(tr)
+            r._check(r.lib.sph_slab_read_owned(r.ctx.h, host_pos.ctypes.data_as(C.c_void_p), None, None), "read_owned")
+        one(0)
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for s in range(e2e_steps):
+            one(s)
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        info = r.info()
+        out = (ms, e2e_ms, info[0], prof, launches, dict(n_local=info[1], halo=info[2:6], z=[sc["z0"], sc["z1"]],
+                                                           n_total=sc["n_total"], e2e_steps=e2e_steps))
+    r.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -183,51 +245,68 @@ def main():
     if world > 1:
         import torch.distributed as dist
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", local))
     L = capi.load_product()
-    p, pos, vel = make_workload(args.workload, L)
-    n = len(pos)
-    ctx = L.create(p, pos, vel, device=local)
-    host_pos = L.pinned_array((n, 4))
-    host_sig = L.pinned_array((100,))
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        ctx.sync()
-
-    # ---- warm-up, then the device-timed region (CUDA events on the library's stream) ----
-    ctx.run_steps(warmup)
-    ctx.profile(True)
-    sampler = ClockSampler(local)
-    barrier()
-    sampler.start()
-    launches0 = ctx.launch_count()
-    ms = ctx.run_steps(steps)
-    launches = ctx.launch_count() - launches0
-    clocks = sampler.stop()
-    prof = ctx.profile_report()
-    ctx.profile(False)
-    barrier()
-    # ---- e2e: host buffers in the loop, wall clock around a synchronous call sequence ----
-    e2e_steps = max(3, min(steps, 10))
-    for s in range(2):
-        ctx.set_muscles(host_sig)
-        ctx.step(sync=False)
-        ctx.read_into("position", host_pos)
-    barrier()
-    t0 = time.perf_counter()
-    for s in range(e2e_steps):
-        host_sig[:] = muscle_signal(s)
-        ctx.set_muscles(host_sig)                 # H2D 400 B (updateMuscleActivityData)
-        ctx.step(sync=False)
-        ctx.read_into("position", host_pos)       # D2H 16 N B (read_position_buffer), blocking
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
-    if dist is not None:
+    slab_info = None
+    if world > 1:
+        sampler = ClockSampler(local)
+        sampler.start()
+        ms, e2e_ms, n, prof, launches, slab_info = run_slab_rank(args, rank, world, local, torch, dist, L, warmup, steps)
+        clocks = sampler.stop()
+        e2e_steps = slab_info["e2e_steps"]
+        p = L.default_params()
+        ctx = None
         t = torch.tensor([ms, e2e_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, e2e_ms = float(t[0]), float(t[1])
-    total = n * world
+        cnt = torch.tensor([n], device="cuda", dtype=torch.int64)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+        total = int(cnt[0])
+    else:
+        L = capi.load_product()
+        p, pos, vel = make_workload(args.workload, L)
+        n = len(pos)
+        ctx = L.create(p, pos, vel, device=local)
+        host_pos = L.pinned_array((n, 4))
+        host_sig = L.pinned_array((100,))
+
+        def barrier():
+            if dist is not None:
+                dist.barrier()
+            ctx.sync()
+
+        # ---- warm-up, then the device-timed region (CUDA events on the library's stream) ----
+        ctx.run_steps(warmup)
+        ctx.profile(True)
+        sampler = ClockSampler(local)
+        barrier()
+        sampler.start()
+        launches0 = ctx.launch_count()
+        ms = ctx.run_steps(steps)
+        launches = ctx.launch_count() - launches0
+        clocks = sampler.stop()
+        prof = ctx.profile_report()
+        ctx.profile(False)
+        barrier()
+        # ---- e2e: host buffers in the loop, wall clock around a synchronous call sequence ----
+        e2e_steps = max(3, min(steps, 10))
+        for s in range(2):
+            ctx.set_muscles(host_sig)
+            ctx.step(sync=False)
+            ctx.read_into("position", host_pos)
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(e2e_steps):
+            host_sig[:] = muscle_signal(s)
+            ctx.set_muscles(host_sig)                 # H2D 400 B (updateMuscleActivityData)
+            ctx.step(sync=False)
+            ctx.read_into("position", host_pos)       # D2H 16 N B (read_position_buffer), blocking
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        if dist is not None:
+            t = torch.tensor([ms, e2e_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, e2e_ms = float(t[0]), float(t[1])
+        total = n
     value = total * steps / (ms * 1e-3)
     peak, peak_src = peaks()
     # dominant kernel of the step
@@ -244,10 +323,11 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
             "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "particles_per_gpu": n, "liquid": int(p.num_liquid),
-                       "boundary": int(p.num_boundary), "grid_cells": int(p.grid_cell_count), "pcisph_iterations": 3,
+            "config": {"workload": args.workload, "particles_per_gpu": n,
+                       "particles_total": total, "slab": slab_info, "pcisph_iterations": 3,
                        "hash_mask": "0xffffffff", "l2": "state (%.1f GB) larger than L2, no flush" % (n * 424 / 1e9),
-                       "multi_gpu": "none" if world == 1 else "independent blocks per rank (no halo exchange yet)"},
+                       "multi_gpu": "none" if world == 1 else
+                       "one fluid, %d z-slabs, ghost layers + per-stage halo refresh + migration over NCCL p2p" % world},
             "clocks": clocks,
             "e2e": {"value": total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 400,
                     "d2h_bytes_per_step": 16 * n, "ms_per_step": e2e_ms, "steps": e2e_steps},
@@ -256,7 +336,8 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"], _, _ = time_cpu(args.cpu_sample, args.cpu_steps, 1)
         print(json.dumps(line), flush=True)
-    ctx.close()
+    if ctx is not None:
+        ctx.close()
     if dist is not None:
         dist.destroy_process_group()
     return 0

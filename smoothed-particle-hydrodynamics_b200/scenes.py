@@ -100,3 +100,64 @@ WORKLOADS = {
     "fluid_256k": (64, 64, 64, None),
     "fluid_32k": (32, 32, 32, None),
 }
+
+
+def boundary_box_slab(bx, by, bz, k0, k1):
+    """The boundary particles of boundary_box(bx, by, bz) whose z index k lies in [k0, k1), with a unique id
+    (i*by + j)*bz + k each — what one slab rank needs, without building the whole box."""
+    k0, k1 = max(0, int(k0)), min(int(bz), int(k1))
+    out = []
+    ii, jj = np.meshgrid(np.arange(bx, dtype=np.int64), np.arange(by, dtype=np.int64), indexing="ij")
+    ii, jj = ii.ravel(), jj.ravel()
+    rim = (ii == 0) | (ii == bx - 1) | (jj == 0) | (jj == by - 1)
+    for k in range(k0, k1):
+        sel = np.ones(ii.size, bool) if (k == 0 or k == bz - 1) else rim
+        idx = np.stack([ii[sel], jj[sel], np.full(int(sel.sum()), k, np.int64)], 1)
+        out.append(idx)
+    idx = np.concatenate(out) if out else np.zeros((0, 3), np.int64)
+    dims = np.array([bx, by, bz], np.int64)
+    f = (idx == 0).astype(np.float32) - (idx == dims - 1).astype(np.float32)
+    nn = np.maximum(np.abs(f).sum(1, keepdims=True), 1)
+    nrm = f * (np.float32(1.0) / np.sqrt(nn.astype(np.float32)))
+    pos = np.empty((len(idx), 4), np.float32)
+    pos[:, :3] = (idx.astype(np.float32) + np.float32(0.5)) * R0
+    pos[:, 3] = np.float32(3.0)
+    vel = np.empty_like(pos)
+    vel[:, :3] = nrm
+    vel[:, 3] = np.float32(3.0)
+    ids = (idx[:, 0] * by + idx[:, 1]) * bz + idx[:, 2]
+    return pos, vel, ids
+
+
+def slab_scene(name, world, rank, seed=12345, jitter_frac=0.05, margin=3):
+    """Weak-scaling scene: the named fluid stacked `world` times along z in one box,
+    cut into `world` slabs of whole hash-cell layers; returns what ONE rank needs:
+    dict(position, velocity, gid, z0, z1, box, n_total, halo_cap, mig_cap). Only this rank's part is generated."""
+    nx, ny, nz, fill = WORKLOADS[name]
+    nzt = nz * world
+    bx, by, bz = nx + 2 * margin, ny + 2 * margin, (nzt if fill is None else fill * world) + 2 * margin
+    bx, by, bz = bx + (bx & 1), by + (by & 1), bz + (bz & 1)
+    gz = int(bz / 2.0) + 1  # (int)((zmax - zmin) / h) + 1 with zmax = (bz/2) * h, owOpenCLSolver.cpp:14-17
+    cell_inv = np.float32(1.0) / (np.float32(2.0) * H)
+    cuts = [0] + [(margin + r * nz) // 4 for r in range(1, world)] + [gz]
+    z0, z1 = cuts[rank], cuts[rank + 1]
+    # lattice / box layers that can fall into cell layers [z0, z1): 4 r0 per cell, one spare layer for the jitter
+    lo, hi = 4 * z0 - 1, 4 * z1 + 1
+    lz0, lz1 = max(0, lo - margin), min(nzt, hi - margin)
+    lp, lv = liquid_block(nx, ny, nzt, (margin, margin, margin), seed, jitter_frac, z_range=(lz0, lz1), nz_total=nzt)
+    ix, iy, iz = np.meshgrid(np.arange(nx, dtype=np.int64), np.arange(ny, dtype=np.int64),
+                             np.arange(lz0, lz1, dtype=np.int64), indexing="ij")
+    lid = ((ix.ravel() * ny + iy.ravel()) * nzt + iz.ravel())
+    bp, bv, bid = boundary_box_slab(bx, by, bz, lo, hi)
+    n_liquid_total = nx * ny * nzt
+    pos, vel = np.concatenate([lp, bp]), np.concatenate([lv, bv])
+    gid = np.concatenate([lid, n_liquid_total + bid])
+    if gid.size and int(gid.max()) >= 2 ** 32:
+        raise ValueError("global ids do not fit 32 bits")
+    cz = (pos[:, 2] * cell_inv).astype(np.int32)
+    own = (cz >= z0) & (cz < z1)
+    n_boundary_total = 2 * bx * by + (bz - 2) * (2 * bx + 2 * by - 4)
+    fullest = 4 * nx * ny + 4 * (2 * bx + 2 * by) + bx * by
+    return dict(position=pos[own], velocity=vel[own], gid=gid[own].astype(np.uint32), z0=z0, z1=z1,
+                box=(bx / 2.0, by / 2.0, bz / 2.0), n_total=n_liquid_total + n_boundary_total,
+                n_liquid=int((pos[own, 3] < 2).sum()), halo_cap=2 * fullest + 1024, mig_cap=fullest // 2 + 1024)
