@@ -162,7 +162,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->prs, c->cellList, c->cellListCount, c->cellCursor, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
+                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -226,7 +226,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->tmpSerial, N));
   A(dalloc(&c->sortedType, N));
   A(dalloc(&c->spT, N));
-  A(dalloc(&c->prs, N));
+  A(dalloc(&c->recA, 2 * N));
+  A(dalloc(&c->recB, 2 * N));
   A(dalloc(&c->cellList, (G < N ? G : N) + 1));
   A(dalloc(&c->cellListCount, 1));
   A(dalloc(&c->cellCursor, 1));

@@ -33,7 +33,7 @@ struct sph_ctx {
   unsigned *tmpSerial;         // N counting-sort scatter target
   float *sortedType;           // N type tag (position.w) in sorted order
   float4 *spT;                 // N sorted (x, y, z, type tag): the copy the force kernels gather
-  float2 *prs;                 // N packed (pressure, rho*) of the fused PCISPH loop
+  float4 *recA, *recB;         // 2N each: 32-byte gather records of the fused path (see ld256, sph_device.cuh)
   unsigned *cellList;          // first non-empty cell of every home block (cell pair) of this step (order arbitrary)
   unsigned *cellListCount;
   unsigned *cellCursor;        // work cursor of the tiled neighbour search

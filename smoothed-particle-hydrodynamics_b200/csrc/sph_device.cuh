@@ -57,6 +57,16 @@ __device__ __forceinline__ float max0(float x) { return (0.f < x) ? x : 0.f; }  
 
 __device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
 
+// Gather RECORDS of the fused path: one 32-byte, 32-byte-aligned record per sorted particle, fetched with a
+// single 256-bit load (LDG.E.256, one L1/L2 sector) instead of two or three 16-byte gathers from separate arrays.
+//   recA[i] = (x, y, z, type | vx, vy, vz, rho(t))   gathered by the viscosity / surface-tension kernel
+//   recB[i] = (x, y, z, type | p, rho*, 0, 0)        gathered by the pressure-force kernel
+__device__ __forceinline__ void ld256(const float4 *rec, float4 &a, float4 &b) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+               : "l"(rec));
+}
+
 // Neighbour ids are kept as int32 in 32x32 tiles: tile t holds particles [32t, 32t+32),
 // element (k, lane) at nb[(t*32 + k)*32 + lane] — a warp reading slot k of its 32
 // particles touches one 128-byte line.

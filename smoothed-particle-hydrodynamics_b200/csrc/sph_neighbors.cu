@@ -50,7 +50,7 @@ __device__ __forceinline__ void neighbor_cells(const DevParams &d, float4 pos, i
 template <bool WITH_DENSITY>
 __device__ __forceinline__ void find_neighbors_one(const DevParams &d, int id, const float4 *__restrict__ sp,
                                                    const unsigned *__restrict__ cellStart, int *__restrict__ nb,
-                                                   float *__restrict__ rho) {
+                                                   float *__restrict__ rho, float4 *__restrict__ recA = nullptr) {
   const float4 pos = sp[id];
   const int myCell = (int)pos.w & d.mask;
   int cells[8];
@@ -116,16 +116,18 @@ __device__ __forceinline__ void find_neighbors_one(const DevParams &d, int id, c
     if (density < (double)d.hScaled6) density = (double)d.hScaled6;
     density *= d.massWpoly6;
     rho[id] = (float)density;
+    if (recA) reinterpret_cast<float *>(recA)[8 * (size_t)id + 7] = (float)density;  // rho slot of the gather record
   }
 }
 
 template <bool WITH_DENSITY>
 __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, const float4 *__restrict__ sp,
                                                                 const unsigned *__restrict__ cellStart,
-                                                                int *__restrict__ nb, float *__restrict__ rho) {
+                                                                int *__restrict__ nb, float *__restrict__ rho,
+                                                                float4 *__restrict__ recA) {
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= d.N) return;
-  find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho);
+  find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
 }
 
 // ---------------------------------------------------------------- tiled path (the product path)
@@ -282,7 +284,8 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
                                                                   const unsigned *__restrict__ cellList,
                                                                   const unsigned *__restrict__ cellListCount,
                                                                   unsigned *__restrict__ cellCursor,
-                                                                  int *__restrict__ nb, float *__restrict__ rho) {
+                                                                  int *__restrict__ nb, float *__restrict__ rho,
+                                                                  float4 *__restrict__ recA) {
   extern __shared__ __align__(16) unsigned char ft_smem[];
   FtShared &S = *reinterpret_cast<FtShared *>(ft_smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -453,7 +456,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         S.rowTid[r] = 255;
       }
       if (tid >= hb) continue;
-      if (S.bad[g]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
+      if (S.bad[g]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA); continue; }
       unsigned *mrow = S.masks + tid * FT_MSTRIDE;
       {  // j == id (:148): the particle's own bit sits in its own cell, the first one visited
         const int selfBit = S.bitLo0[g] + id - ((g & 8) ? hMid : hBeg);
@@ -481,7 +484,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
           nh++;
         }
       }
-      if (nh > FT_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho); continue; }
+      if (nh > FT_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA); continue; }
       // exact distances + 30-bin radial histogram of everything within h (:157-161), in registers:
       // 3 words x 10 bins x 6 bits (a particle keeps <= FT_CAP < 64 hits)
       unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;
@@ -546,6 +549,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         if (density < (double)d.hScaled6) density = (double)d.hScaled6;
         density *= d.massWpoly6;
         rho[id] = (float)density;
+        reinterpret_cast<float *>(recA)[8 * (size_t)id + 7] = (float)density;  // rho slot of the gather record
       }
     }
     cur ^= 1;
@@ -586,7 +590,7 @@ static void launch_tiles(sph_ctx *c) {
   }
   cudaMemsetAsync(c->cellCursor, 0, sizeof(unsigned), c->stream);
   k_neighbor_tiles<WD><<<c->numSMs * ft_ctas_per_sm, FT_THREADS, sizeof(FtShared), c->stream>>>(
-      c->d, c->sortedPosition, c->cellStart, c->cellList, c->cellListCount, c->cellCursor, c->nbIds, c->rho);
+      c->d, c->sortedPosition, c->cellStart, c->cellList, c->cellListCount, c->cellCursor, c->nbIds, c->rho, c->recA);
 }
 
 void launch_find_neighbors(sph_ctx *c, bool with_density) {
@@ -594,9 +598,9 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   if (c->force_generic_neighbors || c->d.gx < 4 || c->d.gy < 3 || c->d.gz < 3) {
     int blocks = (c->d.N + 127) / 128;
     if (with_density)
-      k_find_neighbors_generic<true><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho);
+      k_find_neighbors_generic<true><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho, c->recA);
     else
-      k_find_neighbors_generic<false><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho);
+      k_find_neighbors_generic<false><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho, nullptr);
     return;
   }
   // persistent CTAs (one resident wave); home blocks handed out through an atomic cursor over cellList

@@ -94,13 +94,22 @@ __global__ void __launch_bounds__(256) k_slab_iota(int *__restrict__ dst, int n,
 template <int FIELD, bool PACK>
 __global__ void __launch_bounds__(256) k_slab_halo(int n, const int *__restrict__ list, int first,
                                                    const unsigned *__restrict__ back, float *__restrict__ rho,
-                                                   float2 *__restrict__ prs, float4 *__restrict__ spPred,
+                                                   float4 *__restrict__ recA, float4 *__restrict__ recB,
+                                                   float4 *__restrict__ spPred,
                                                    void *__restrict__ buf) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const unsigned sid = back[list ? list[i] : first + i];
-  if (FIELD == 0) { float *b = (float *)buf; if (PACK) b[i] = rho[sid]; else rho[sid] = b[i]; }
-  if (FIELD == 1) { float2 *b = (float2 *)buf; if (PACK) b[i] = prs[sid]; else prs[sid] = b[i]; }
+  if (FIELD == 0) {  // rho(t): the array and the rho slot of the gather record
+    float *b = (float *)buf;
+    if (PACK) b[i] = rho[sid];
+    else { rho[sid] = b[i]; reinterpret_cast<float *>(recA)[8 * (size_t)sid + 7] = b[i]; }
+  }
+  if (FIELD == 1) {  // (p, rho*): second half of the pressure-force record
+    float2 *b = (float2 *)buf;
+    float4 *q = recB + 2 * (size_t)sid + 1;
+    if (PACK) b[i] = make_float2(q->x, q->y); else *q = make_float4(b[i].x, b[i].y, 0.f, 0.f);
+  }
   if (FIELD == 2) { float4 *b = (float4 *)buf; if (PACK) b[i] = spPred[sid]; else spPred[sid] = b[i]; }
 }
 
@@ -225,7 +234,7 @@ static int halo(sph_ctx *c, int field, int side, void *buf, bool pack) {
   const int *list = pack ? s->sendList[side] : nullptr;
   const int first = s->recvStart[side];
   float4 *pred = c->sortedPosition + c->d.N;
-#define H(F, P) k_slab_halo<F, P><<<nblk(n), 256, 0, c->stream>>>(n, list, first, c->particleIndexBack, c->rho, c->prs, pred, buf)
+#define H(F, P) k_slab_halo<F, P><<<nblk(n), 256, 0, c->stream>>>(n, list, first, c->particleIndexBack, c->rho, c->recA, c->recB, pred, buf)
   if (pack) { if (field == 0) H(0, true); else if (field == 1) H(1, true); else H(2, true); }
   else { if (field == 0) H(0, false); else if (field == 1) H(1, false); else H(2, false); }
 #undef H

@@ -145,7 +145,8 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
                                                       float4 *__restrict__ sortedVelocity,
                                                       float *__restrict__ sortedType, float4 *__restrict__ spT, unsigned *__restrict__ cellList,
                                                       unsigned *__restrict__ cellListCount,
-                                                      const unsigned *__restrict__ rankKey) {
+                                                      const unsigned *__restrict__ rankKey,
+                                                      float4 *__restrict__ recA, float4 *__restrict__ recB) {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= d.N) return;
   unsigned serial = tmpSerial[s];
@@ -170,8 +171,13 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
     float4 p = position[serial];
     sortedType[dst] = p.w;
     spT[dst] = p;
+    const float4 v = velocity[serial];
+    recA[2 * (size_t)dst] = p;
+    recA[2 * (size_t)dst + 1] = f4(v.x, v.y, v.z, 0.f);  // .w = rho(t), set by the neighbour search
+    recB[2 * (size_t)dst] = p;
+    recB[2 * (size_t)dst + 1] = f4(0.f, 0.f, 0.f, 0.f);
     p.w = (float)(int)cell;
-    sortedVelocity[dst] = velocity[serial];
+    sortedVelocity[dst] = v;
     sortedPosition[dst] = p;
     particleIndexBack[serial] = dst;
   }
@@ -228,12 +234,12 @@ void launch_sort(sph_ctx *c, bool fuse_reorder) {
     k_rank_reorder<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                    c->particleIndex, c->particleIndexBack, c->position,
                                                                    c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey);
+                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey, c->recA, c->recB);
   else
     k_rank_reorder<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                     c->particleIndex, c->particleIndexBack, c->position,
                                                                     c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey);
+                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey, c->recA, c->recB);
 }
 
 void launch_reorder(sph_ctx *c) {
