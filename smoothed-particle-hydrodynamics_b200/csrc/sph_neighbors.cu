@@ -422,7 +422,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         const unsigned short *wtab = S.wordOff[gg];
         const int nch = S.nWords[gg];
         unsigned keep0 = 0, keep1 = 0, keep2 = 0, keep3 = 0;
-#pragma unroll 2
+#pragma unroll 4
         for (int c = 0; c < nch; c++) {
           const unsigned off = wtab[c];
           const float cx = *reinterpret_cast<const float *>(xb + off);
@@ -488,10 +488,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
       // exact distances + 30-bin radial histogram of everything within h (:157-161), in registers:
       // 3 words x 10 bins x 6 bits (a particle keeps <= FT_CAP < 64 hits)
       unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;
-      for (int t = 0; t < nh; t++) {
-        const int s = S.hits[t][tid] & 0xfff;
-        float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
-        float dd = ex * ex + ey * ey + ez * ez;
+      auto hist_add = [&](float dd) {
         if (dd <= h2) {
           // bin (int)(sqrtf(dd)*30/h): approximate guess, made exact with the host-built thresholds
           float sq;
@@ -506,6 +503,23 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
             hist1 += (w == 1) ? inc : 0ull;
             hist2 += (w == 2) ? inc : 0ull;
           }
+        }
+      };
+      {  // two hits per pass: their loads and distance chains are independent
+        int t = 0;
+        for (; t + 1 < nh; t += 2) {
+          const int s0 = S.hits[t][tid] & 0xfff, s1 = S.hits[t + 1][tid] & 0xfff;
+          const float ex0 = pos.x - S.X[s0], ey0 = pos.y - S.Y[s0], ez0 = pos.z - S.Z[s0];
+          const float ex1 = pos.x - S.X[s1], ey1 = pos.y - S.Y[s1], ez1 = pos.z - S.Z[s1];
+          const float dd0 = ex0 * ex0 + ey0 * ey0 + ez0 * ez0;
+          const float dd1 = ex1 * ex1 + ey1 * ey1 + ez1 * ez1;
+          hist_add(dd0);
+          hist_add(dd1);
+        }
+        if (t < nh) {
+          const int s0 = S.hits[t][tid] & 0xfff;
+          const float ex0 = pos.x - S.X[s0], ey0 = pos.y - S.Y[s0], ez0 = pos.z - S.Z[s0];
+          hist_add(ex0 * ex0 + ey0 * ey0 + ez0 * ez0);
         }
       }
       // radius threshold (:310-324)
@@ -525,19 +539,34 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
       // first 32 hits within r_thr, in scan order (:166-174) + rho(t)
       int found = 0;
       double density = 0.0;
-      for (int t = 0; t < nh; t++) {
-        const unsigned hv = S.hits[t][tid];
-        const int s = hv & 0xfff;
-        float ex = pos.x - S.X[s], ey = pos.y - S.Y[s], ez = pos.z - S.Z[s];
-        float dd = ex * ex + ey * ey + ez * ez;
-        if (dd <= r2) {
-          S.hits[found][tid] = (unsigned short)hv;  // in-place compaction: found <= t
+      auto take = [&](unsigned hv, float dd) {
+        if (found < SPH_NB && dd <= r2) {
+          S.hits[found][tid] = (unsigned short)hv;  // in-place compaction: found <= index of hv
           if (WITH_DENSITY) {
             float r = sqrtf(dd) * d.simScale;
             float rr = r * r;
             density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
           }
-          if (++found == SPH_NB) break;
+          found++;
+        }
+      };
+      {  // two hits per pass (independent loads and distance chains), taken in scan order
+        int t = 0;
+        for (; t + 1 < nh && found < SPH_NB; t += 2) {
+          const unsigned hv0 = S.hits[t][tid], hv1 = S.hits[t + 1][tid];
+          const int s0 = hv0 & 0xfff, s1 = hv1 & 0xfff;
+          const float ex0 = pos.x - S.X[s0], ey0 = pos.y - S.Y[s0], ez0 = pos.z - S.Z[s0];
+          const float ex1 = pos.x - S.X[s1], ey1 = pos.y - S.Y[s1], ez1 = pos.z - S.Z[s1];
+          const float dd0 = ex0 * ex0 + ey0 * ey0 + ez0 * ez0;
+          const float dd1 = ex1 * ex1 + ey1 * ey1 + ez1 * ez1;
+          take(hv0, dd0);
+          take(hv1, dd1);
+        }
+        if (t < nh && found < SPH_NB) {
+          const unsigned hv0 = S.hits[t][tid];
+          const int s0 = hv0 & 0xfff;
+          const float ex0 = pos.x - S.X[s0], ey0 = pos.y - S.Y[s0], ez0 = pos.z - S.Z[s0];
+          take(hv0, ex0 * ex0 + ey0 * ey0 + ez0 * ez0);
         }
       }
 #pragma unroll 8
