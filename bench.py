@@ -90,7 +90,17 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+CONFIG_A = os.path.join(ROOT, "tests", "golden", "configA.npz")  # the reference's shipped pure-liquid scene
+
+
 def make_workload(name, lib):
+    if name == "config_a":  # BASELINE config 0: positionPureLiquid.txt / velocityPureLiquid.txt, 36h x 24h x 54h, 16-bit mask
+        z = np.load(CONFIG_A)
+        pos, vel = z["position"], z["velocity"]
+        p = lib.default_params(box=(36, 24, 54))
+        t = pos[:, 3].astype(np.int32)
+        p.particle_count, p.num_liquid, p.num_boundary = len(pos), int((t == 1).sum()), int((t == 3).sum())
+        return p, pos, vel
     nx, ny, nz, fill = scenes.WORKLOADS[name]
     pos, vel, box = scenes.fluid_box(nx, ny, nz, fill_z=fill)
     p = lib.default_params(box=box)
@@ -224,9 +234,9 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="fluid_8m", choices=sorted(scenes.WORKLOADS))
-    ap.add_argument("--cpu-sample", default="fluid_256k", choices=sorted(scenes.WORKLOADS))
-    ap.add_argument("--cpu-steps", type=int, default=8)
+    ap.add_argument("--workload", default="fluid_8m", choices=sorted(scenes.WORKLOADS) + ["config_a"])
+    ap.add_argument("--cpu-sample", default="fluid_2m", choices=sorted(scenes.WORKLOADS) + ["config_a"])
+    ap.add_argument("--cpu-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -325,7 +335,8 @@ def main():
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "particles_per_gpu": n,
                        "particles_total": total, "slab": slab_info, "pcisph_iterations": 3,
-                       "hash_mask": "0xffffffff", "l2": "state (%.1f GB) larger than L2, no flush" % (n * 424 / 1e9),
+                       "hash_mask": "0xffffffff", "l2": ("state (%.1f GB) larger than L2, no flush" % (n * 424 / 1e9)) if n * 424 > 2.5e8 else
+                       "state (%.0f MB) FITS in L2: not a bench configuration, reported for the config-A target only" % (n * 424 / 1e6),
                        "multi_gpu": "none" if world == 1 else
                        "one fluid, %d z-slabs, ghost layers + per-stage halo refresh + migration over NCCL p2p" % world},
             "clocks": clocks,

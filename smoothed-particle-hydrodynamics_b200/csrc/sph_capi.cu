@@ -162,7 +162,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
+                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -230,7 +230,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->recB, 2 * N));
   A(dalloc(&c->cellList, (G < N ? G : N) + 1));
   A(dalloc(&c->cellListCount, 1));
-  A(dalloc(&c->cellCursor, 1));
+  A(dalloc(&c->cellCursor, 2));
+  A(dalloc(&c->fnDeferred, N));
   A(dalloc(&c->scanState, (size_t)c->scanTiles));
   A(dalloc(&c->scanTicket, 1));
   if (ok) A(cudaMemcpy(c->position, pos4, 16 * N, cudaMemcpyHostToDevice));   // owOpenCLSolver.cpp:65
@@ -349,7 +350,7 @@ int sph_step(sph_ctx *c) {
     { ProfScope s(c, last ? PK_PRESSURE_FORCE_INTEGRATE : PK_PRESSURE_FORCE); launch_pressure_force(c, last ? 2 : 1); }
   }
   { ProfScope s(c, PK_MEMBRANES); launch_membrane_interaction(c, true); }
-  c->launches += 8 + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
+  c->launches += 9 + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
   return check_launch(c, false);
 }
 
@@ -368,7 +369,7 @@ int sph_step_part(sph_ctx *c, int part) {
       { ProfScope s(c, PK_HASH); launch_hash_count(c, false); }
       { ProfScope s(c, PK_SORT); launch_sort(c, true); }
       { ProfScope s(c, PK_NEIGHBORS); launch_find_neighbors(c, true); }
-      c->launches += 5;
+      c->launches += 6;
       break;
     case 1:
       { ProfScope s(c, PK_FORCES); launch_forces(c, true); }

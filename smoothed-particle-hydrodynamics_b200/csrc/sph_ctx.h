@@ -36,7 +36,8 @@ struct sph_ctx {
   float4 *recA, *recB;         // 2N each: 32-byte gather records of the fused path (see ld256, sph_device.cuh)
   unsigned *cellList;          // first non-empty cell of every home block (cell pair) of this step (order arbitrary)
   unsigned *cellListCount;
-  unsigned *cellCursor;        // work cursor of the tiled neighbour search
+  unsigned *cellCursor;        // [0] work cursor of the tiled neighbour search, [1] length of fnDeferred
+  int *fnDeferred;             // N: particles whose neighbourhood does not fit the tile tables (generic scan)
   int numSMs;
   bool force_generic_neighbors; // SPH_GENERIC_NEIGHBORS=1: one-thread-per-particle search (debug / A-B)
   unsigned long long *scanState;  // decoupled look-back tile states

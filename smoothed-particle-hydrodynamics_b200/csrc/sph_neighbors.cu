@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
                                                                   const unsigned *__restrict__ cellListCount,
                                                                   unsigned *__restrict__ cellCursor,
                                                                   int *__restrict__ nb, float *__restrict__ rho,
-                                                                  float4 *__restrict__ recA) {
+                                                                  float4 *__restrict__ recA, int *__restrict__ deferred) {
   extern __shared__ __align__(16) unsigned char ft_smem[];
   FtShared &S = *reinterpret_cast<FtShared *>(ft_smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -456,7 +456,9 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         S.rowTid[r] = 255;
       }
       if (tid >= hb) continue;
-      if (S.bad[g]) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA); continue; }
+      // neighbourhoods the tables cannot hold go to the deferred list: k_neighbors_deferred scans them with
+      // one thread each, spread over the whole GPU, instead of stalling this CTA (cellCursor[1] = list length)
+      if (S.bad[g]) { deferred[atomicAdd(cellCursor + 1, 1u)] = id; continue; }
       unsigned *mrow = S.masks + tid * FT_MSTRIDE;
       {  // j == id (:148): the particle's own bit sits in its own cell, the first one visited
         const int selfBit = S.bitLo0[g] + id - ((g & 8) ? hMid : hBeg);
@@ -484,7 +486,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
           nh++;
         }
       }
-      if (nh > FT_CAP) { find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA); continue; }
+      if (nh > FT_CAP) { deferred[atomicAdd(cellCursor + 1, 1u)] = id; continue; }
       // exact distances + 30-bin radial histogram of everything within h (:157-161), in registers:
       // 3 words x 10 bins x 6 bits (a particle keeps <= FT_CAP < 64 hits)
       unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;
@@ -607,6 +609,17 @@ void launch_clear_neighbors(sph_ctx *c) {
   k_clear_neighbors<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->nbIds, n);
 }
 
+template <bool WITH_DENSITY>
+__global__ void __launch_bounds__(128) k_neighbors_deferred(DevParams d, const float4 *__restrict__ sp,
+                                                            const unsigned *__restrict__ cellStart,
+                                                            const unsigned *__restrict__ cellCursor,
+                                                            const int *__restrict__ deferred, int *__restrict__ nb,
+                                                            float *__restrict__ rho, float4 *__restrict__ recA) {
+  const int n = (int)cellCursor[1];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    find_neighbors_one<WITH_DENSITY>(d, deferred[i], sp, cellStart, nb, rho, recA);
+}
+
 static int ft_ctas_per_sm = 0;
 template <bool WD>
 static void launch_tiles(sph_ctx *c) {
@@ -617,9 +630,11 @@ static void launch_tiles(sph_ctx *c) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_neighbor_tiles<true>, FT_THREADS, sizeof(FtShared));
     ft_ctas_per_sm = occ < 1 ? 1 : occ;
   }
-  cudaMemsetAsync(c->cellCursor, 0, sizeof(unsigned), c->stream);
+  cudaMemsetAsync(c->cellCursor, 0, 2 * sizeof(unsigned), c->stream);  // [0] work cursor, [1] deferred count
   k_neighbor_tiles<WD><<<c->numSMs * ft_ctas_per_sm, FT_THREADS, sizeof(FtShared), c->stream>>>(
-      c->d, c->sortedPosition, c->cellStart, c->cellList, c->cellListCount, c->cellCursor, c->nbIds, c->rho, c->recA);
+      c->d, c->sortedPosition, c->cellStart, c->cellList, c->cellListCount, c->cellCursor, c->nbIds, c->rho, c->recA, c->fnDeferred);
+  k_neighbors_deferred<WD><<<c->numSMs * 8, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->cellCursor,
+                                                                 c->fnDeferred, c->nbIds, c->rho, c->recA);
 }
 
 void launch_find_neighbors(sph_ctx *c, bool with_density) {
