@@ -50,6 +50,26 @@ KERNEL_BYTES = {
 }
 
 
+# profile name -> kernel whose ncu capture (profiles/*_ncu_full_summary.json) gives the measured DRAM traffic per launch
+NCU_KERNEL = {"find_neighbors+density": "k_neighbor_tiles<1>", "pressure_force+predict": "k_pressure_force<1>",
+              "pressure_force+integrate": "k_pressure_force<2>", "predict_density+correct_pressure": "k_predict_density<1>"}
+
+
+def measured_traffic(kernel, particles):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this same workload (None when the capture is for another particle count)."""
+    import glob
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_full_summary.json")), reverse=True):
+        try:
+            j = json.load(open(f))
+        except (OSError, ValueError):
+            continue
+        k = j.get("kernels", {}).get(NCU_KERNEL.get(kernel, ""))
+        if k and j.get("particles") == particles:
+            return k["dram_bytes_per_launch"], os.path.basename(f)
+    return None, None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -325,8 +345,9 @@ def main():
     if top:
         avg_ms = prof[top]["ms"] / prof[top]["calls"]
         ach = KERNEL_BYTES.get(top, 0) * n / (avg_ms * 1e-3) / 1e9
+        traffic, traffic_src = measured_traffic(top, n) if world == 1 else (None, None)
         roof = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "avg_launch_ms": avg_ms,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "avg_launch_ms": avg_ms,
                 "algorithmic_bytes_per_particle": KERNEL_BYTES.get(top, 0),
                 "step_achieved": value / world * B_REF / 1e9, "step_frac": value / world * B_REF / 1e9 / peak,
                 "kernel_share_of_step": {k: v["ms"] / (ms if ms else 1) for k, v in prof.items()}}
