@@ -309,6 +309,8 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
     const FtHalo &H = S.halo[cur];
     if (!H.valid) break;
     const int hBeg = H.hBeg, hMid = H.hMid, hEnd = H.hEnd, blockBad = H.bad;
+    // the first batch's home particle of this thread: requested now, needed after the tables and the staging
+    const float4 posFirst = (hBeg + tid < hEnd) ? ldg4(sp + hBeg + tid) : f4(0.f, 0.f, 0.f, 0.f);
     // ---- group tables of the block (depend on the cell table only)
     if (tid < FT_GROUPS * 4) {  // thread (g, r): the mask words of run r
       const int g = tid >> 2, r = tid & 3;
@@ -355,15 +357,28 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         S.bad[g] = (blockBad || q.wOff[4] > FT_NCH || sg > FT_NSEG) ? 1 : 0;
       }
     }
-    // ---- stage the positions of the 36 cells
+    // ---- stage the positions of the 36 cells: two cells per pass, six loads in flight per lane
     if (!blockBad) {
+      auto put = [&](int s, const float4 &q) { S.X[s] = q.x; S.Y[s] = q.y; S.Z[s] = q.z; };
 #pragma unroll 1
-      for (int t = warp; t < FT_NCELL; t += FT_WARPS) {
-        const int g0 = H.gStart[t], n = H.cnt[t], s0 = H.sStart[t];
-        for (int i = lane; i < n; i += 32) {
-          const float4 q = ldg4(sp + g0 + i);
-          S.X[s0 + i] = q.x; S.Y[s0 + i] = q.y; S.Z[s0 + i] = q.z;
+      for (int t = warp; t < FT_NCELL; t += 2 * FT_WARPS) {
+        const int t2 = t + FT_WARPS;
+        const int g0 = H.gStart[t] + lane, n0 = H.cnt[t] - lane, s0 = H.sStart[t] + lane;
+        int g1 = 0, n1 = 0, s1 = 0;
+        if (t2 < FT_NCELL) { g1 = H.gStart[t2] + lane; n1 = H.cnt[t2] - lane; s1 = H.sStart[t2] + lane; }
+        float4 q[6];
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+          if (32 * c < n0) q[c] = ldg4(sp + g0 + 32 * c);
+          if (32 * c < n1) q[3 + c] = ldg4(sp + g1 + 32 * c);
         }
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+          if (32 * c < n0) put(s0 + 32 * c, q[c]);
+          if (32 * c < n1) put(s1 + 32 * c, q[3 + c]);
+        }
+        for (int i = 96; i < n0; i += 32) put(s0 + i, ldg4(sp + g0 + i));
+        for (int i = 96; i < n1; i += 32) put(s1 + i, ldg4(sp + g1 + i));
       }
     }
     for (int b0 = hBeg; b0 < hEnd; b0 += FT_ROWS) {
@@ -374,7 +389,7 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
       float4 pos = f4(0.f, 0.f, 0.f, 0.f);
       int g = 0, rankInG = 0;
       if (tid < hb) {
-        pos = sp[id];
+        pos = (b0 == hBeg) ? posFirst : sp[id];
         float cfx = (float)(int)(pos.x * d.cellSizeInv) * d.cellSize;
         float cfy = (float)(int)(pos.y * d.cellSizeInv) * d.cellSize;
         float cfz = (float)(int)(pos.z * d.cellSizeInv) * d.cellSize;
