@@ -234,6 +234,12 @@ const char *sph_slab_last_error(void);
 int sph_step_part(sph_ctx *ctx, int part);
 /* Run the context on a caller-owned CUDA stream (cudaStream_t), NULL = its own stream again. */
 int sph_set_stream(sph_ctx *ctx, void *cuda_stream);
+/* Pipelined read-back of SPH_BUF_POSITION or SPH_BUF_VELOCITY (owOpenCLSolver::read_position_buffer,
+ * owOpenCLSolver.h:60, called at owPhysicsFluidSimulator.cpp:115, without its blocking wait): the copy to `dst` (pinned host memory) starts when the
+ * work queued so far is done and overlaps the next sph_step, whose integration kernel waits for it.
+ * sph_read_end blocks until the bytes have arrived. One read in flight per context. */
+int sph_read_begin(sph_ctx *ctx, int buffer_id, void *dst, size_t bytes);
+int sph_read_end(sph_ctx *ctx);
 /* Raw device memory for exchange buffers; synchronous copy between any host / device pointers. */
 void *sph_device_alloc(size_t bytes);
 void sph_device_free(void *p);

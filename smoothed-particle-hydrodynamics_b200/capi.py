@@ -100,6 +100,9 @@ class SphLib:
         L.sph_last_error.restype = C.c_char_p
         L.sph_backend.restype = C.c_char_p
         self.has_instrumentation = hasattr(L, "sph_run_steps")
+        if hasattr(L, "sph_read_begin"):   # product only: pipelined read-back
+            L.sph_read_begin.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t]
+            L.sph_read_end.argtypes = [C.c_void_p]
         if self.has_instrumentation:  # CUDA library only
             L.sph_run_steps.argtypes = [C.c_void_p, C.c_int, P(C.c_float)]
             L.sph_profile_enable.argtypes = [C.c_void_p, C.c_int]
@@ -235,6 +238,13 @@ class SphContext:
         bid = BUFFERS[name][0]
         self.L.check(self.L.lib.sph_read(self.h, bid, _ptr(out), out.nbytes), "sph_read(%s)" % name)
         return out
+
+    def read_begin(self, name, out):
+        """Start a device-to-host copy of position / velocity into `out` (pinned) that overlaps the next step."""
+        self.L.check(self.L.lib.sph_read_begin(self.h, BUFFERS[name][0], _ptr(out), out.nbytes), "sph_read_begin(%s)" % name)
+
+    def read_end(self):
+        self.L.check(self.L.lib.sph_read_end(self.h), "sph_read_end")
 
     def write(self, name, arr):
         bid, dt, _ = BUFFERS[name]

@@ -166,6 +166,16 @@ void sph_destroy(sph_ctx *c) {
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
+  if (c->copyStream) {
+    cudaStreamSynchronize(c->copyStream);
+    cudaStreamDestroy(c->copyStream);
+    cudaEventDestroy(c->evReadReady);
+    cudaEventDestroy(c->evReadDone);
+  }
+  if (c->sigRing) {
+    cudaFreeHost(c->sigRing);
+    for (cudaEvent_t e : c->sigDone) cudaEventDestroy(e);
+  }
   if (c->ownStream) cudaStreamDestroy(c->ownStream);
   delete c;
 }
@@ -490,8 +500,20 @@ int sph_sync(sph_ctx *c) {
 int sph_set_muscles(sph_ctx *c, const float *signal, int n) {
   if (!c || !signal || n < 0 || n > c->p.muscle_count) return fail(SPH_E_INVALID, "sph_set_muscles: bad arguments");
   CU(cudaSetDevice(c->device));
-  CU(cudaMemcpyAsync(c->muscle, signal, 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
+  if (n == 0) return 0;
+  // copy into the next slot of a pinned ring, upload from there in stream order: the caller's buffer is free on
+  // return (the reference's blocking write, owOpenCLSolver.cpp updateMuscleActivityData) without draining the stream
+  const size_t slotFloats = (size_t)(c->p.muscle_count > 0 ? c->p.muscle_count : 1);
+  if (!c->sigRing) {
+    CU(cudaMallocHost((void **)&c->sigRing, 4 * slotFloats * sizeof(float)));
+    for (cudaEvent_t &e : c->sigDone) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  const unsigned slot = c->sigNext++ & 3u;
+  CU(cudaEventSynchronize(c->sigDone[slot]));  // four uploads ago: long done
+  float *stage = c->sigRing + slot * slotFloats;
+  memcpy(stage, signal, 4 * (size_t)n);
+  CU(cudaMemcpyAsync(c->muscle, stage, 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaEventRecord(c->sigDone[slot], c->stream));
   return 0;
 }
 
@@ -551,6 +573,41 @@ int sph_read(sph_ctx *c, int id, void *dst, size_t bytes) {
   return 0;
 }
 
+// Pipelined read-back of POSITION or VELOCITY: the copy starts when the work queued so far is done and runs on a
+// second stream, so the caller can queue the next sph_step right away; the kernel of that step which rewrites the
+// buffer (integration, the step's last kernel) waits for the copy. sph_read_end blocks until the bytes are in dst
+// (pinned memory, or the copy is not asynchronous). One read in flight per context.
+int sph_read_begin(sph_ctx *c, int id, void *dst, size_t bytes) {
+  if (!c || !dst) return fail(SPH_E_INVALID, "sph_read_begin: null");
+  if (id != SPH_BUF_POSITION && id != SPH_BUF_VELOCITY) return fail(SPH_E_UNSUPPORTED, "sph_read_begin: position or velocity only");
+  if (c->slab) return fail(SPH_E_UNSUPPORTED, "sph_read_begin: slab ranks read through sph_slab_read_owned");
+  if (c->readPending) return fail(SPH_E_INVALID, "sph_read_begin: a read is already in flight");
+  size_t have = 0;
+  void *src = dev_ptr(c, id, &have);
+  if (bytes > have) return fail(SPH_E_SIZE, "sph_read_begin: too many bytes");
+  CU(cudaSetDevice(c->device));
+  if (!c->copyStream) {
+    CU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->evReadReady, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->evReadDone, cudaEventDisableTiming));
+  }
+  CU(cudaEventRecord(c->evReadReady, c->stream));
+  CU(cudaStreamWaitEvent(c->copyStream, c->evReadReady, 0));
+  CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->copyStream));
+  CU(cudaEventRecord(c->evReadDone, c->copyStream));
+  c->readPending = 1;
+  return 0;
+}
+
+int sph_read_end(sph_ctx *c) {
+  if (!c) return fail(SPH_E_INVALID, "sph_read_end: null");
+  if (!c->readPending) return 0;
+  CU(cudaSetDevice(c->device));
+  CU(cudaEventSynchronize(c->evReadDone));
+  c->readPending = 0;
+  return 0;
+}
+
 int sph_write(sph_ctx *c, int id, const void *src, size_t bytes) {
   if (!c || !src) return fail(SPH_E_INVALID, "sph_write: null");
   if (id != SPH_BUF_POSITION && id != SPH_BUF_VELOCITY) return fail(SPH_E_UNSUPPORTED, "sph_write: buffer not writable");
@@ -558,6 +615,7 @@ int sph_write(sph_ctx *c, int id, const void *src, size_t bytes) {
   void *dst = dev_ptr(c, id, &have);
   if (bytes > have) return fail(SPH_E_SIZE, "sph_write: too many bytes");
   CU(cudaSetDevice(c->device));
+  read_fence(c);
   CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;

@@ -53,7 +53,22 @@ struct sph_ctx {
   unsigned *rankKey;           // in-cell ranking key per original index (global ids of a slab rank); null = the index itself
   cudaStream_t ownStream;      // the stream created with the context (c->stream may be replaced by sph_set_stream)
   long long launches;          // kernels launched by sph_step so far
+  // pipelined read-back (sph_read_begin / sph_read_end): a device-to-host copy of position or velocity that
+  // runs on its own stream while the next step computes; the integration kernel waits for it (read_fence)
+  cudaStream_t copyStream;
+  cudaEvent_t evReadReady, evReadDone;
+  int readPending;
+  // muscle signal upload: staged through a small pinned ring so that sph_set_muscles neither waits for the
+  // step in flight nor depends on the caller's buffer after it returns
+  float *sigRing;
+  cudaEvent_t sigDone[4];
+  unsigned sigNext;
 };
+
+// order the next writer of position / velocity after a pending pipelined read of them
+static inline void read_fence(sph_ctx *c) {
+  if (c->readPending) cudaStreamWaitEvent(c->stream, c->evReadDone, 0);
+}
 
 // sph_sort.cu
 void launch_hash_count(sph_ctx *c, bool write_pairs);

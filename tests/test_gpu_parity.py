@@ -171,3 +171,35 @@ def test_read_write_roundtrip_and_errors(P):
         ctx.write("rho", np.zeros(4, np.float32))
     with pytest.raises(capi.SphError):
         P.create(P.default_params(), np.zeros((0, 4), np.float32), np.zeros((0, 4), np.float32))
+
+
+def test_pipelined_readback_matches_blocking_reads(P):
+    """sph_read_begin / sph_read_end: the copy of step k's positions overlaps step k+1 (whose integration kernel
+    waits for it) and must deliver exactly what a blocking read after step k sees."""
+    pos, vel = common.synthetic_block(24, 20, 30, (32, 28, 80), seed=11)
+    cfg = dict(params=common.fill_counts(P.default_params(box=(16, 14, 40)), pos), position=pos, velocity=vel)
+    steps = 5
+    a = common.create(P, cfg)
+    want = []
+    for _ in range(steps):
+        a.step()
+        want.append(a.read("position", a.N))
+    a.close()
+    b = common.create(P, cfg)
+    bufs = [P.pinned_array((b.N, 4)), P.pinned_array((b.N, 4))]
+    got = []
+    for s in range(steps):
+        b.step(sync=False)
+        b.read_end()                       # step s-1 has arrived
+        if s:
+            got.append(bufs[(s - 1) & 1].copy())
+        b.read_begin("position", bufs[s & 1])
+        with pytest.raises(capi.SphError):
+            b.read_begin("position", bufs[s & 1])   # one read in flight
+    b.read_end()
+    got.append(bufs[(steps - 1) & 1].copy())
+    with pytest.raises(capi.SphError):
+        b.read_begin("rho", bufs[0])
+    b.close()
+    for s in range(steps):
+        assert common.first_mismatch(got[s], want[s]) is None, "step %d" % s
