@@ -213,7 +213,11 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   c->scanTiles = sph_scan_tiles_for((int)G + 1);
   cudaDeviceGetAttribute(&c->numSMs, cudaDevAttrMultiProcessorCount, device);
   if (c->numSMs <= 0) c->numSMs = 148;
-  { const char *e = getenv("SPH_GENERIC_NEIGHBORS"); c->force_generic_neighbors = e && e[0] == '1'; }
+  {  // neighbour search path: auto (tiles for large fluids), or forced for A-B runs and the parity tests
+    const char *e = getenv("SPH_GENERIC_NEIGHBORS"), *q = getenv("SPH_NEIGHBOR_PATH");
+    c->force_generic_neighbors = (e && e[0] == '1') || (q && !strcmp(q, "generic"));
+    c->force_tiled_neighbors = q && !strcmp(q, "tiles");
+  }
   bool ok = true;
 #define A(x) ok = ok && ((e = (x)) == cudaSuccess)
   A(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));

@@ -39,7 +39,8 @@ struct sph_ctx {
   unsigned *cellCursor;        // [0] work cursor of the tiled neighbour search, [1] length of fnDeferred
   int *fnDeferred;             // N: particles whose neighbourhood does not fit the tile tables (generic scan)
   int numSMs;
-  bool force_generic_neighbors; // SPH_GENERIC_NEIGHBORS=1: one-thread-per-particle search (debug / A-B)
+  bool force_generic_neighbors; // SPH_NEIGHBOR_PATH=generic (or SPH_GENERIC_NEIGHBORS=1): one thread per particle
+  bool force_tiled_neighbors;   // SPH_NEIGHBOR_PATH=tiles: the tile kernel whatever the particle count (grid permitting)
   unsigned long long *scanState;  // decoupled look-back tile states
   unsigned *scanTicket;
   int scanTiles;

@@ -6,6 +6,8 @@ is possible because the kernels keep the reference's operation order and are bui
 contraction. Compared against (a) the C oracle run live on the same inputs and (b) the committed
 digests produced by the reference's own kernels (tests/golden/digests.json).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -34,6 +36,19 @@ STAGE_OUTPUTS = {
     "MEMBRANE_INTERACTION": ["position"],
     "MEMBRANE_FINALIZE": ["position"],
 }
+
+
+@pytest.fixture(scope="module", autouse=True, params=["tiles", "generic"])
+def neighbor_path(request):
+    """Every parity test runs twice: with the tile kernel forced (the path large fluids take; the test scenes are
+    below the size where the library picks it by itself) and with the one-thread-per-particle scan."""
+    old = os.environ.get("SPH_NEIGHBOR_PATH")
+    os.environ["SPH_NEIGHBOR_PATH"] = request.param
+    yield request.param
+    if old is None:
+        os.environ.pop("SPH_NEIGHBOR_PATH", None)
+    else:
+        os.environ["SPH_NEIGHBOR_PATH"] = old
 
 
 @pytest.fixture(scope="module")

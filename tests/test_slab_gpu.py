@@ -12,6 +12,19 @@ pytestmark = pytest.mark.gpu
 slab = importlib.import_module(common.PKG + ".slab")
 
 
+@pytest.fixture(scope="module", autouse=True)
+def tiled_neighbors():
+    """Slab ranks of a bench-sized fluid take the tile kernel; the test scenes are small, so force it."""
+    import os
+    old = os.environ.get("SPH_NEIGHBOR_PATH")
+    os.environ["SPH_NEIGHBOR_PATH"] = "tiles"
+    yield
+    if old is None:
+        os.environ.pop("SPH_NEIGHBOR_PATH", None)
+    else:
+        os.environ["SPH_NEIGHBOR_PATH"] = old
+
+
 @pytest.fixture(scope="module")
 def P():
     return common.product_lib()
