@@ -222,6 +222,7 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
 #define A(x) ok = ok && ((e = (x)) == cudaSuccess)
   A(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   c->ownStream = c->stream;
+  c->dispDirty = true;
   A(dalloc(&c->position, 2 * N));
   A(dalloc(&c->velocity, 2 * N));
   A(dalloc(&c->particleIndex, N));
@@ -349,6 +350,22 @@ struct ProfScope {
   }
 };
 
+// Membrane interaction + finalize of the fused step. Without a membrane list the kernel would only zero the
+// displacement half of `position` (clearMembraneBuffers) and add +0 (finalize): the integration kernel has
+// folded the add in, and the displacement half is zeroed once per upload instead of once per step.
+static int fused_membranes(sph_ctx *c) {
+  if (c->has_pml) {
+    ProfScope s(c, PK_MEMBRANES);
+    launch_membrane_interaction(c, true);
+    return 1;
+  }
+  if (c->dispDirty) {
+    cudaMemsetAsync(c->position + c->d.N, 0, 16 * (size_t)c->d.N, c->stream);
+    c->dispDirty = false;
+  }
+  return 0;
+}
+
 int sph_step(sph_ctx *c) {
   if (!c) return fail(SPH_E_INVALID, "null ctx");
   CU(cudaSetDevice(c->device));
@@ -363,8 +380,8 @@ int sph_step(sph_ctx *c) {
     const bool last = it + 1 == iters;
     { ProfScope s(c, last ? PK_PRESSURE_FORCE_INTEGRATE : PK_PRESSURE_FORCE); launch_pressure_force(c, last ? 2 : 1); }
   }
-  { ProfScope s(c, PK_MEMBRANES); launch_membrane_interaction(c, true); }
-  c->launches += 9 + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
+  const int mem = fused_membranes(c);
+  c->launches += 8 + mem + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
   return check_launch(c, false);
 }
 
@@ -395,8 +412,7 @@ int sph_step_part(sph_ctx *c, int part) {
     case 3: { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); } c->launches++; break;
     case 4:
       { ProfScope s(c, PK_PRESSURE_FORCE_INTEGRATE); launch_pressure_force(c, 2); }
-      { ProfScope s(c, PK_MEMBRANES); launch_membrane_interaction(c, true); }
-      c->launches += 2;
+      c->launches += 1 + fused_membranes(c);
       break;
     default: return fail(SPH_E_INVALID, "sph_step_part: unknown part");
   }
@@ -620,6 +636,7 @@ int sph_write(sph_ctx *c, int id, const void *src, size_t bytes) {
   if (bytes > have) return fail(SPH_E_SIZE, "sph_write: too many bytes");
   CU(cudaSetDevice(c->device));
   read_fence(c);
+  if (id == SPH_BUF_POSITION) c->dispDirty = true;
   CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;

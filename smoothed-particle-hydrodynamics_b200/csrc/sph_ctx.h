@@ -49,6 +49,7 @@ struct sph_ctx {
   float4 *readScratch;
   bool has_elastic, has_membranes, has_pml;
   bool neighbors_valid;
+  bool dispDirty;              // the displacement half of `position` may hold non-zero values (fresh upload)
   void *profiler;              // Profiler* when per-kernel event timing is on
   SlabState *slab;             // non-null: this context is one slab rank of a multi-device fluid (sph_slab.cu)
   unsigned *rankKey;           // in-cell ranking key per original index (global ids of a slab rank); null = the index itself
