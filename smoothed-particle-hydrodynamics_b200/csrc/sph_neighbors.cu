@@ -508,26 +508,22 @@ __global__ void __launch_bounds__(FT_THREADS, 3) k_neighbor_tiles(DevParams d, c
         const int selfBit = S.bitLo0[g] + id - ((g & 8) ? hMid : hBeg);
         mrow[selfBit >> 5] &= ~(1u << (selfBit & 31));
       }
-      // walk the row through the segment table -> hit list in scan order. One flat loop: an iteration
-      // either opens the next segment or takes one hit of the current one.
+      // walk the row through the segment table -> hit list in scan order
       int nh = 0;
       {
         const unsigned *segM = S.segMask[g], *segI = S.segInfo[g];
         const int nSeg = S.nSeg[g];
-        int sg = -1;
-        unsigned m = 0u, hbase = 0u;
-        while (true) {
-          if (m == 0u) {
-            if (++sg >= nSeg) break;
-            const unsigned info = segI[sg];
-            m = mrow[info >> 16] & segM[sg];
-            hbase = (((info >> 13) & 7u) << 12) + (info & 0x1fffu) - 32u;  // (k << 12) | staged index of bit 0
-            continue;
+#pragma unroll 1
+        for (int sg = 0; sg < nSeg; sg++) {
+          const unsigned info = segI[sg];
+          unsigned m = mrow[info >> 16] & segM[sg];
+          const unsigned hbase = (((info >> 13) & 7u) << 12) + (info & 0x1fffu) - 32u;  // (k << 12) | staged index of bit 0
+          while (m) {
+            const unsigned hv = hbase + (unsigned)__ffs(m) - 1u;
+            m &= m - 1;
+            if (nh < FT_CAP) S.hits[nh][tid] = (unsigned short)hv;
+            nh++;
           }
-          const unsigned hv = hbase + (unsigned)__ffs(m) - 1u;
-          m &= m - 1;
-          if (nh < FT_CAP) S.hits[nh][tid] = (unsigned short)hv;
-          nh++;
         }
       }
       if (nh > FT_CAP) { deferred[atomicAdd(cellCursor + 1, 1u)] = id; continue; }
