@@ -228,6 +228,8 @@ int sph_slab_pack(sph_ctx *ctx, int field, int side, void *buf);
 int sph_slab_unpack(sph_ctx *ctx, int field, int side, const void *buf);
 /* Owned particles (any order) and their global ids, to host memory. Synchronous. */
 int sph_slab_read_owned(sph_ctx *ctx, float *pos4, float *vel4, uint32_t *gid);
+/* Pipelined form for the owned positions (pinned pos4): overlaps the next step; complete it with sph_read_end. */
+int sph_slab_read_owned_begin(sph_ctx *ctx, float *pos4);
 const char *sph_slab_last_error(void);
 /* The fused step in the five pieces between which a slab rank refreshes its ghosts:
  * 0 | rho | 1 | (p,rho*) | 2 | x* | 3 | (p,rho*) | 2 | x* | 3 | (p,rho*) | 4   for max_iteration = 3. */

@@ -616,6 +616,7 @@ int sph_read_begin(sph_ctx *c, int id, void *dst, size_t bytes) {
   CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->copyStream));
   CU(cudaEventRecord(c->evReadDone, c->copyStream));
   c->readPending = 1;
+  c->readSrc = src;
   return 0;
 }
 

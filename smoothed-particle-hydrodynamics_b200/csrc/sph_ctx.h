@@ -60,6 +60,7 @@ struct sph_ctx {
   cudaStream_t copyStream;
   cudaEvent_t evReadReady, evReadDone;
   int readPending;
+  const void *readSrc;         // device buffer the pending read copies from
   // muscle signal upload: staged through a small pinned ring so that sph_set_muscles neither waits for the
   // step in flight nor depends on the caller's buffer after it returns
   float *sigRing;

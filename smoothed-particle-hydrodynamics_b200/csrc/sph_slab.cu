@@ -197,6 +197,7 @@ int sph_slab_absorb(sph_ctx *c, const void *mig_from_down, const void *ghost_fro
   a.src[4] = (const SlabRec *)ghost_from_up; a.n[4] = ghU;
   a.src[5] = s->myMig[1]; a.n[5] = s->migOut[1];
   a.base = keep;
+  if (c->readPending && c->readSrc == (const void *)s->posAlt) read_fence(c);  // a pipelined read still copies from the buffer rebuilt now
   const int total = inD + inU + nGhost;
   if (total > 0) k_slab_append<<<nblk(total), 256, 0, c->stream>>>(a, s->posAlt, s->velAlt, s->gidAlt);
   if (inD > 0) k_slab_iota<<<nblk(inD), 256, 0, c->stream>>>(s->sendList[0] + s->ghostOut[0], inD, keep);
@@ -257,6 +258,26 @@ int sph_slab_read_owned(sph_ctx *c, float *pos4, float *vel4, uint32_t *gid) {
   if (pos4) SCU(cudaMemcpy(pos4, c->position, 16 * n, cudaMemcpyDeviceToHost));
   if (vel4) SCU(cudaMemcpy(vel4, c->velocity, 16 * n, cudaMemcpyDeviceToHost));
   if (gid) SCU(cudaMemcpy(gid, s->gid, 4 * n, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// Pipelined variant for the positions: the copy of this step's owned particles overlaps the next step (it reads the
+// buffer that the next absorb only reads and the one after rebuilds). Finish with sph_read_end.
+int sph_slab_read_owned_begin(sph_ctx *c, float *pos4) {
+  if (!c || !c->slab || !pos4) return slab_fail("sph_slab_read_owned_begin: not a slab context / null");
+  if (c->readPending) return slab_fail("sph_slab_read_owned_begin: a read is already in flight");
+  SCU(cudaSetDevice(c->device));
+  if (!c->copyStream) {
+    SCU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
+    SCU(cudaEventCreateWithFlags(&c->evReadReady, cudaEventDisableTiming));
+    SCU(cudaEventCreateWithFlags(&c->evReadDone, cudaEventDisableTiming));
+  }
+  SCU(cudaEventRecord(c->evReadReady, c->stream));
+  SCU(cudaStreamWaitEvent(c->copyStream, c->evReadReady, 0));
+  SCU(cudaMemcpyAsync(pos4, c->position, 16 * (size_t)c->slab->nOwn, cudaMemcpyDeviceToHost, c->copyStream));
+  SCU(cudaEventRecord(c->evReadDone, c->copyStream));
+  c->readPending = 1;
+  c->readSrc = c->position;
   return 0;
 }
 

@@ -93,6 +93,7 @@ class SlabRank:
         L.sph_slab_pack.argtypes = [V, I, I, V]
         L.sph_slab_unpack.argtypes = [V, I, I, V]
         L.sph_slab_read_owned.argtypes = [V, V, V, V]
+        L.sph_slab_read_owned_begin.argtypes = [V, V]
         L.sph_slab_last_error.restype = C.c_char_p
         L.sph_step_part.argtypes = [V, I]
         L.sph_set_stream.argtypes = [V, V]
@@ -161,6 +162,11 @@ class SlabRank:
                                                  vel.ctypes.data_as(C.c_void_p), gid.ctypes.data_as(C.c_void_p)),
                     "sph_slab_read_owned")
         return pos, vel, gid
+
+    def read_owned_begin(self, out):
+        """Pipelined read of the owned positions into `out` (pinned, >= n_owned rows); finish with ctx.read_end()."""
+        self._check(self.lib.sph_slab_read_owned_begin(self.ctx.h, out.ctypes.data_as(C.c_void_p)),
+                    "sph_slab_read_owned_begin")
 
     def close(self):
         self.ctx.close()

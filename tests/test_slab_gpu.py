@@ -65,6 +65,12 @@ def run_slabs(P, p, pos, vel, world, steps):
     for _ in range(steps):
         slab.slab_step(tr)
         moved += sum(c[0] + c[2] for c in [r.counts for r in ranks])
+    for r in ranks:   # the pipelined read of the owned positions delivers what the blocking read does
+        want = r.read_owned()[0]
+        buf = P.pinned_array((len(want) + 8, 4))
+        r.read_owned_begin(buf)
+        r.ctx.read_end()
+        assert np.array_equal(buf[:len(want)], want)
     out = slab.gather_owned(ranks, len(pos))
     infos = [r.info() for r in ranks]
     for r in ranks:
