@@ -158,6 +158,7 @@ int sph_slab_classify(sph_ctx *c, void *mig_down, void *ghost_down, void *mig_up
   SlabState *s = c->slab;
   SCU(cudaSetDevice(c->device));
   SCU(cudaMemsetAsync(s->counters, 0, 32, c->stream));
+  if (c->readPending && c->readSrc == (const void *)s->posAlt) read_fence(c);  // a pipelined read still copies from the buffer rebuilt now
   SlabGeom g = {s->z0, s->z1, s->hasDown, s->hasUp, s->nOwn, s->migCap, s->haloCap};
   k_slab_classify<<<nblk(s->nOwn), 256, 0, c->stream>>>(c->d, g, c->position, c->velocity, s->gid, s->posAlt, s->velAlt,
                                                         s->gidAlt, (SlabRec *)mig_down, (SlabRec *)ghost_down,
@@ -197,7 +198,6 @@ int sph_slab_absorb(sph_ctx *c, const void *mig_from_down, const void *ghost_fro
   a.src[4] = (const SlabRec *)ghost_from_up; a.n[4] = ghU;
   a.src[5] = s->myMig[1]; a.n[5] = s->migOut[1];
   a.base = keep;
-  if (c->readPending && c->readSrc == (const void *)s->posAlt) read_fence(c);  // a pipelined read still copies from the buffer rebuilt now
   const int total = inD + inU + nGhost;
   if (total > 0) k_slab_append<<<nblk(total), 256, 0, c->stream>>>(a, s->posAlt, s->velAlt, s->gidAlt);
   if (inD > 0) k_slab_iota<<<nblk(inD), 256, 0, c->stream>>>(s->sendList[0] + s->ghostOut[0], inD, keep);
