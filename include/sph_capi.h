@@ -228,6 +228,9 @@ int sph_slab_pack(sph_ctx *ctx, int field, int side, void *buf);
 int sph_slab_unpack(sph_ctx *ctx, int field, int side, const void *buf);
 /* Owned particles (any order) and their global ids, to host memory. Synchronous. */
 int sph_slab_read_owned(sph_ctx *ctx, float *pos4, float *vel4, uint32_t *gid);
+/* Load balancing: move the slab's faces by at most one cell layer each; the layer that falls outside travels to the
+ * neighbour as ordinary migrants in the next sph_slab_classify. Both ranks sharing a face call it before the same step. */
+int sph_slab_set_cut(sph_ctx *ctx, int z0, int z1);
 /* Pipelined form for the owned positions (pinned pos4): overlaps the next step; complete it with sph_read_end. */
 int sph_slab_read_owned_begin(sph_ctx *ctx, float *pos4);
 const char *sph_slab_last_error(void);

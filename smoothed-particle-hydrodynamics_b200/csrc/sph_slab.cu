@@ -29,9 +29,10 @@ struct SlabState {
   int migOut[2], ghostOut[2];
   const SlabRec *myMig[2];
   int nSend[2], nRecv[2], recvStart[2];
+  int recut;                      // the faces moved since the last classify (sph_slab_set_cut)
 };
 
-struct SlabGeom { int z0, z1, hasDown, hasUp, nOwn, migCap, haloCap; };
+struct SlabGeom { int z0, z1, hasDown, hasUp, nOwn, migCap, haloCap, slack; };
 
 __global__ void __launch_bounds__(256) k_slab_classify(DevParams d, SlabGeom s, const float4 *__restrict__ pos,
                                                        const float4 *__restrict__ vel, const unsigned *__restrict__ gid,
@@ -47,7 +48,8 @@ __global__ void __launch_bounds__(256) k_slab_classify(DevParams d, SlabGeom s, 
   const int cz = (int)(p.z * d.cellSizeInv);  // the z factor of hashParticles' cell id, sphFluid.cl:361-365
   SlabRec r;
   r.pos = p; r.vel = v; r.tag = make_float4(__uint_as_float(g), 0.f, 0.f, 0.f);
-  if ((s.hasDown && cz < s.z0 - 1) || (s.hasUp && cz > s.z1)) atomicOr(&counters[5], 1);  // moved more than one layer
+  // moved more than one layer (two right after a re-cut, which hands a whole layer to the neighbour)
+  if ((s.hasDown && cz < s.z0 - 1 - s.slack) || (s.hasUp && cz > s.z1 + s.slack)) atomicOr(&counters[5], 1);
   if (s.hasDown && cz < s.z0) {
     const int slot = atomicAdd(&counters[0], 1);
     if (slot < s.migCap) migD[slot] = r; else atomicOr(&counters[5], 2);
@@ -159,7 +161,8 @@ int sph_slab_classify(sph_ctx *c, void *mig_down, void *ghost_down, void *mig_up
   SCU(cudaSetDevice(c->device));
   SCU(cudaMemsetAsync(s->counters, 0, 32, c->stream));
   if (c->readPending && c->readSrc == (const void *)s->posAlt) read_fence(c);  // a pipelined read still copies from the buffer rebuilt now
-  SlabGeom g = {s->z0, s->z1, s->hasDown, s->hasUp, s->nOwn, s->migCap, s->haloCap};
+  SlabGeom g = {s->z0, s->z1, s->hasDown, s->hasUp, s->nOwn, s->migCap, s->haloCap, s->recut};
+  s->recut = 0;
   k_slab_classify<<<nblk(s->nOwn), 256, 0, c->stream>>>(c->d, g, c->position, c->velocity, s->gid, s->posAlt, s->velAlt,
                                                         s->gidAlt, (SlabRec *)mig_down, (SlabRec *)ghost_down,
                                                         (SlabRec *)mig_up, (SlabRec *)ghost_up, s->sendList[0],
@@ -258,6 +261,20 @@ int sph_slab_read_owned(sph_ctx *c, float *pos4, float *vel4, uint32_t *gid) {
   if (pos4) SCU(cudaMemcpy(pos4, c->position, 16 * n, cudaMemcpyDeviceToHost));
   if (vel4) SCU(cudaMemcpy(vel4, c->velocity, 16 * n, cudaMemcpyDeviceToHost));
   if (gid) SCU(cudaMemcpy(gid, s->gid, 4 * n, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+// Move the slab's faces (load balancing): the next classify hands the layers that fell outside to the neighbours as
+// ordinary migrants. One layer per face and call; both ranks that share a face must move it before the same step.
+int sph_slab_set_cut(sph_ctx *c, int z0, int z1) {
+  if (!c || !c->slab) return slab_fail("not a slab context");
+  SlabState *s = c->slab;
+  if (z1 - z0 < 2) return slab_fail("sph_slab_set_cut: a slab keeps at least 2 cell layers");
+  if (abs(z0 - s->z0) > 1 || abs(z1 - s->z1) > 1) return slab_fail("sph_slab_set_cut: a face moves one layer at a time");
+  if ((!s->hasDown && z0 != s->z0) || (!s->hasUp && z1 != s->z1)) return slab_fail("sph_slab_set_cut: outer faces are fixed");
+  if (z0 != s->z0 || z1 != s->z1) s->recut = 1;
+  s->z0 = z0;
+  s->z1 = z1;
   return 0;
 }
 

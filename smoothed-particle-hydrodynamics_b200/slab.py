@@ -51,6 +51,7 @@ class SlabRank:
         self.L, self.lib = lib, lib.lib
         self.index, self.world = index, world
         self.has = [index > 0, index < world - 1]
+        self.z0, self.z1 = int(z0), int(z1)
         n = len(position)
         halo_guess = max(1024, int(2.5 * n / max(1, z1 - z0)))      # ~ one cell layer, with head-room
         self.halo_cap = int(halo_cap or halo_guess)
@@ -94,6 +95,7 @@ class SlabRank:
         L.sph_slab_unpack.argtypes = [V, I, I, V]
         L.sph_slab_read_owned.argtypes = [V, V, V, V]
         L.sph_slab_read_owned_begin.argtypes = [V, V]
+        L.sph_slab_set_cut.argtypes = [V, I, I]
         L.sph_slab_last_error.restype = C.c_char_p
         L.sph_step_part.argtypes = [V, I]
         L.sph_set_stream.argtypes = [V, V]
@@ -133,6 +135,13 @@ class SlabRank:
                                              b["mig_in", UP].ptr, b["ghost_in", UP].ptr, inc), "sph_slab_absorb")
         info = self.info()
         self.n_send, self.n_recv = info[2:4], info[4:6]
+
+    def set_cut(self, z0, z1):
+        self._check(self.lib.sph_slab_set_cut(self.ctx.h, int(z0), int(z1)), "sph_slab_set_cut")
+        self.z0, self.z1 = int(z0), int(z1)
+
+    def n_owned(self):
+        return self.info()[0]
 
     def info(self):
         out = (C.c_int * 6)()
@@ -208,6 +217,10 @@ class LoopbackTransport:
                 nb = self.ranks[i - 1]
                 nb.copy(nb.buf[kind_in, UP], r.buf[kind_out, DOWN], sizes[i][DOWN])
 
+    def all_gather(self, rows):
+        """rows[r] = a few ints of local rank r -> the rows of all ranks, in rank order."""
+        return [list(x) for x in rows]
+
     def exchange_records(self, counts, incoming):
         rec = self.ranks[0].rec
         self._move("mig_out", "mig_in", [[c[0] * rec, c[2] * rec] for c in counts])
@@ -264,6 +277,13 @@ class DistTransport:
         self._p2p(sends, recvs)
         return [in_dn.tolist() + in_up.tolist()]
 
+    def all_gather(self, rows):
+        torch = self.torch
+        mine = torch.tensor(rows[0], dtype=torch.int64)
+        out = [torch.zeros_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(out, mine)   # CPU tensors: the gloo side of the process group
+        return [t.tolist() for t in out]
+
     def _move(self, kind_out, kind_in, out_bytes, in_bytes):
         r = self.ranks[0]
         sends, recvs = [], []
@@ -319,6 +339,36 @@ def slab_step(transport):
         halo(PRS)
     for r in ranks:
         r.part(4)
+
+
+def plan_cuts(cuts, owned):
+    """New face positions from the current ones and the owned counts of all ranks: a face moves one layer towards
+    the fuller of its two slabs when they differ by more than two average layers, and never leaves a slab with
+    fewer than 2 layers. Pure function of its arguments: every rank computes the same plan."""
+    new, n = list(cuts), [float(x) for x in owned]
+    for b in range(1, len(cuts) - 1):
+        per_layer = (n[b - 1] + n[b]) / max(1, new[b + 1] - new[b - 1])
+        if n[b - 1] - n[b] > 2 * per_layer and new[b] - new[b - 1] > 2:
+            new[b] -= 1
+            n[b - 1] -= per_layer
+            n[b] += per_layer
+        elif n[b] - n[b - 1] > 2 * per_layer and new[b + 1] - new[b] > 2:
+            new[b] += 1
+            n[b] -= per_layer
+            n[b - 1] += per_layer
+    return new
+
+
+def rebalance(transport):
+    """Re-cut the slabs by particle count (call between steps, on every rank, at the same step). Returns True
+    when a face moved; the layer that changed hands migrates in the next slab_step."""
+    ranks = transport.ranks
+    table = transport.all_gather([[r.z0, r.z1, r.n_owned()] for r in ranks])
+    cuts = [row[0] for row in table] + [table[-1][1]]
+    new = plan_cuts(cuts, [row[2] for row in table])
+    for r in ranks:
+        r.set_cut(new[r.index], new[r.index + 1])
+    return new != cuts
 
 
 def split_fluid(params, position, world):

@@ -57,6 +57,12 @@ class OracleSlabRank:
         raw = rec.view(np.uint8).reshape(-1)
         self._np(kind, side)[:len(raw)] = raw
 
+    def set_cut(self, z0, z1):
+        self.z0, self.z1 = int(z0), int(z1)
+
+    def n_owned(self):
+        return len(self.gid)
+
     def classify(self):
         cz = slab.cell_layer(self.pos[:, 2], self.params.hash_grid_cell_size_inv)
         down = (cz < self.z0) if self.has[DOWN] else np.zeros(len(cz), bool)

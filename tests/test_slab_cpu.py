@@ -74,6 +74,44 @@ def test_slab_protocol_loopback_three_ranks_matches_single_domain():
     assert common.first_mismatch(sv, ref_vel) is None
 
 
+def slabs_for_cuts(p, pos, cuts):
+    cz = slab.cell_layer(pos[:, 2], p.hash_grid_cell_size_inv)
+    return [(cuts[r], cuts[r + 1], np.nonzero((cz >= cuts[r]) & (cz < cuts[r + 1]))[0]) for r in range(len(cuts) - 1)]
+
+
+def test_plan_cuts_moves_one_layer_towards_the_fuller_slab():
+    assert slab.plan_cuts([0, 10, 20], [1000, 1000]) == [0, 10, 20]
+    assert slab.plan_cuts([0, 10, 20], [3000, 1000]) == [0, 9, 20]
+    assert slab.plan_cuts([0, 10, 20], [1000, 3000]) == [0, 11, 20]
+    assert slab.plan_cuts([0, 2, 20], [9000, 1000]) == [0, 2, 20]          # never below 2 layers
+    assert slab.plan_cuts([0, 4, 8, 12], [4000, 1000, 4000]) == [0, 3, 9, 12]
+
+
+def test_slab_recut_loopback_hands_layers_over_and_matches_single_domain():
+    """Uneven initial cut + rebalance() before every step: whole layers change owner while the fluid moves; the
+    result per global id stays the single-domain one."""
+    O = common.oracle_lib()
+    pos, vel = scene()
+    p = params_for(O, pos)
+    ref_pos, ref_vel = single_domain(O, p, pos, vel, STEPS)
+    gz = int(p.grid_cells_z)
+    cuts = [0, 2, 8, gz]                 # the fluid fills layers 0..9: most of it starts on the middle rank
+    ranks = [slab_oracle.OracleSlabRank(O, p, pos[own], vel[own], own, z0, z1, r, 3, host_alloc())
+             for r, (z0, z1, own) in enumerate(slabs_for_cuts(p, pos, cuts))]
+    tr = slab.LoopbackTransport(ranks)
+    moved_faces = 0
+    history = []
+    for _ in range(STEPS):
+        moved_faces += bool(slab.rebalance(tr))
+        slab.slab_step(tr)
+        history.append([r.n_owned() for r in ranks])
+    sp, sv = slab.gather_owned(ranks, len(pos))
+    assert moved_faces >= 2, "the faces never moved: %s" % history
+    assert [r.z0 for r in ranks][1] > 2, "the lower face did not advance into the crowded slab"
+    assert common.first_mismatch(sp, ref_pos) is None
+    assert common.first_mismatch(sv, ref_vel) is None
+
+
 def _gloo_worker(rank, world, port, outdir):
     import torch.distributed as dist
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -82,14 +120,17 @@ def _gloo_worker(rank, world, port, outdir):
         O = common.oracle_lib()
         pos, vel = scene()
         p = params_for(O, pos)
-        slabs, _ = slab.split_fluid(p, pos, world)
-        z0, z1, own = slabs[rank]
+        # uneven cut (most of the fluid on rank 1) + rebalance() every step: the face walks towards the balance
+        # point, whole layers travel as migrants; the counts for the plan go through all_gather on gloo
+        z0, z1, own = slabs_for_cuts(p, pos, [0, 2, int(p.grid_cells_z)])[rank]
         r = slab_oracle.OracleSlabRank(O, p, pos[own], vel[own], own, z0, z1, rank, world, host_alloc())
         tr = slab.DistTransport(r)
         moved = 0
         for _ in range(STEPS):
+            slab.rebalance(tr)
             slab.slab_step(tr)
             moved += r.counts[0] + r.counts[2]
+        assert (r.z1 if rank == 0 else r.z0) > 2, "the face never moved"
         op, ov, og = r.read_owned()
         np.savez(os.path.join(outdir, "rank%d.npz" % rank), pos=op, vel=ov, gid=og, moved=moved)
         dist.barrier()

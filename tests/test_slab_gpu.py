@@ -104,3 +104,46 @@ def test_slab_fluid_at_rest_and_errors(P):
     p16 = common.fill_counts(P.default_params(box=(10, 10, 32)), pos)
     with pytest.raises(RuntimeError):
         slab.SlabRank(P, p16, pos, vel, np.arange(len(pos), dtype=np.uint32), 0, 8, 0, 1)
+
+
+def test_slab_recut_hands_layers_over(P):
+    """Load balancing: an uneven initial cut, slab.rebalance() before every step, and one face forced back and forth
+    every step. Whole cell layers change owner while the fluid moves; per global id the result stays bit-identical
+    to the single-device run."""
+    pos, vel = moving_fluid(seed=3)
+    p = make(P, pos, vel)
+    steps = 10
+    ref_pos, ref_vel = run_single(P, p, pos, vel, steps)
+    cz = slab.cell_layer(pos[:, 2], p.hash_grid_cell_size_inv)
+    top = int(cz.max()) + 1
+    cuts = [0, 3, top - 4, int(p.grid_cells_z)]   # most of the fluid starts on the middle rank
+    fullest = int(np.bincount(cz).max())
+    caps = dict(halo_cap=2 * fullest + 1024, mig_cap=fullest + 1024)
+    ranks = []
+    for r in range(3):
+        own = np.nonzero((cz >= cuts[r]) & (cz < cuts[r + 1]))[0]
+        ranks.append(slab.SlabRank(P, p, pos[own], vel[own], own.astype(np.uint32), cuts[r], cuts[r + 1], r, 3,
+                                   capacity=len(pos) + 4 * caps["halo_cap"], **caps))
+    tr = slab.LoopbackTransport(ranks)
+    moves, sizes = 0, []
+    for s in range(steps):
+        if s < 6:
+            moves += bool(slab.rebalance(tr))
+        else:   # then push the lower face up and down regardless of balance
+            d = 1 if s % 2 == 0 else -1
+            ranks[0].set_cut(ranks[0].z0, ranks[0].z1 + d)
+            ranks[1].set_cut(ranks[1].z0 + d, ranks[1].z1)
+        slab.slab_step(tr)
+        sizes.append([r.n_owned() for r in ranks])
+    sp, sv = slab.gather_owned(ranks, len(pos))
+    for r in ranks:
+        r.close()
+    assert moves >= 2, "rebalance never moved a face: %s" % sizes
+    assert common.first_mismatch(sp, ref_pos) is None, sizes
+    assert common.first_mismatch(sv, ref_vel) is None
+    with pytest.raises(RuntimeError):   # two layers at once are refused
+        rr = slab.SlabRank(P, p, pos, vel, np.arange(len(pos), dtype=np.uint32), 0, 8, 0, 2, **caps)
+        try:
+            rr.set_cut(0, 10)
+        finally:
+            rr.close()
