@@ -113,7 +113,20 @@ class ClockSampler:
 CONFIG_A = os.path.join(ROOT, "tests", "golden", "configA.npz")  # the reference's shipped pure-liquid scene
 
 
+CONFIG_B = os.path.join(ROOT, "tests", "golden", "worm.npz")     # the reference generator's worm scene (fixture)
+EXTRA = {}   # workload name -> dict(elastic=, membranes=, pml=) for scenes with elastic matter
+
+
 def make_workload(name, lib):
+    if name == "config_b":  # BASELINE config 1 of the reference: elastic worm body, membranes, muscles, 16-bit mask
+        z = np.load(CONFIG_B)
+        pos, vel = z["position"], z["velocity"]
+        p = lib.default_params()
+        t = pos[:, 3].astype(np.int32)
+        p.particle_count, p.num_liquid, p.num_boundary = len(pos), int((t == 1).sum()), int((t == 3).sum())
+        p.num_elastic, p.num_membranes = int((t == 2).sum()), int(np.asarray(z["membraneData"]).reshape(-1, 3).shape[0])
+        EXTRA[name] = dict(elastic=z["elasticConnectionsData"], membranes=z["membraneData"], pml=z["particleMembranesList"])
+        return p, pos, vel
     if name == "config_a":  # BASELINE config 0: positionPureLiquid.txt / velocityPureLiquid.txt, 36h x 24h x 54h, 16-bit mask
         z = np.load(CONFIG_A)
         pos, vel = z["position"], z["velocity"]
@@ -155,7 +168,7 @@ def time_cpu(sample, steps, warmup):
     cores = os.cpu_count() or 1
     set_threads(cores)
     p, pos, vel = make_workload(sample, L)
-    ctx = L.create(p, pos, vel)
+    ctx = L.create(p, pos, vel, **EXTRA.get(sample, {}))
     for _ in range(warmup):
         ctx.step()
     t0 = time.perf_counter()
@@ -274,8 +287,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="fluid_8m", choices=sorted(scenes.WORKLOADS) + ["config_a"])
-    ap.add_argument("--cpu-sample", default="fluid_2m", choices=sorted(scenes.WORKLOADS) + ["config_a"])
+    ap.add_argument("--workload", default="fluid_8m", choices=sorted(scenes.WORKLOADS) + ["config_a", "config_b"])
+    ap.add_argument("--cpu-sample", default="fluid_2m", choices=sorted(scenes.WORKLOADS) + ["config_a", "config_b"])
     ap.add_argument("--cpu-steps", type=int, default=30)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -320,7 +333,7 @@ def main():
         L = capi.load_product()
         p, pos, vel = make_workload(args.workload, L)
         n = len(pos)
-        ctx = L.create(p, pos, vel, device=local)
+        ctx = L.create(p, pos, vel, device=local, **EXTRA.get(args.workload, {}))
         host_pos = L.pinned_array((n, 4))
         host_sig = L.pinned_array((100,))
 

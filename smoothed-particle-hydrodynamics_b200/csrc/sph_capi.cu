@@ -172,6 +172,10 @@ void sph_destroy(sph_ctx *c) {
     cudaEventDestroy(c->evReadReady);
     cudaEventDestroy(c->evReadDone);
   }
+  if (c->hostDeferred) {
+    cudaFreeHost(c->hostDeferred);
+    cudaEventDestroy(c->evDeferred);
+  }
   if (c->sigRing) {
     cudaFreeHost(c->sigRing);
     for (cudaEvent_t e : c->sigDone) cudaEventDestroy(e);

@@ -40,6 +40,13 @@ struct sph_ctx {
   int *fnDeferred;             // N: particles whose neighbourhood does not fit the tile tables (generic scan)
   int numSMs;
   bool force_generic_neighbors; // SPH_NEIGHBOR_PATH=generic (or SPH_GENERIC_NEIGHBORS=1): one thread per particle
+  // auto mode: the tile kernel's deferred count of an earlier step (read back without a sync) decides whether the
+  // fluid suits the tiles; above 10 % deferred particles, or below 64 particles per home block, the plain scan runs
+  // for the next 64 steps, then the tiles retry
+  unsigned *hostDeferred;       // pinned, 2 words: deferred particles, home blocks
+  cudaEvent_t evDeferred;
+  bool deferredPending;
+  int genericHold;
   bool force_tiled_neighbors;   // SPH_NEIGHBOR_PATH=tiles: the tile kernel whatever the particle count (grid permitting)
   unsigned long long *scanState;  // decoupled look-back tile states
   unsigned *scanTicket;

@@ -682,7 +682,20 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   // Below ~1000 home blocks (two per resident CTA) its persistent CTAs do not balance and the plain scan wins
   // (config A, 61 k particles: 0.17 ms against 0.32 ms).
   const bool tilesFit = c->d.gx >= 4 && c->d.gy >= 3 && c->d.gz >= 3;
-  const bool useTiles = tilesFit && !c->force_generic_neighbors && (c->force_tiled_neighbors || c->d.N >= 131072);
+  bool useTiles = tilesFit && !c->force_generic_neighbors && (c->force_tiled_neighbors || c->d.N >= 131072);
+  const bool adaptive = useTiles && !c->force_tiled_neighbors;
+  if (adaptive) {
+    // The tile kernel pays a fixed price per home block (cell table, staging of 36 cells) and a high one per
+    // deferred particle. Scenes with many thinly populated blocks (the worm scene: long box, wall-only cells; 0.25 ms
+    // with the plain scan against 0.46 ms) or many overflowing neighbourhoods are faster with the plain scan. Both
+    // paths give identical lists, so switching is free of side effects. Statistics of an earlier step, no sync.
+    if (c->deferredPending && cudaEventQuery(c->evDeferred) == cudaSuccess) {
+      c->deferredPending = false;
+      const double deferred = (double)c->hostDeferred[0], blocks = (double)c->hostDeferred[1], n = (double)c->d.N;
+      if (deferred > 0.10 * n || n < 64.0 * blocks) c->genericHold = 64;
+    }
+    if (c->genericHold > 0) { c->genericHold--; useTiles = false; }
+  }
   if (!useTiles) {
     int blocks = (c->d.N + 127) / 128;
     if (with_density)
@@ -693,6 +706,16 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   }
   // persistent CTAs (one resident wave); home blocks handed out through an atomic cursor over cellList
   if (with_density) launch_tiles<true>(c); else launch_tiles<false>(c);
+  if (adaptive && !c->deferredPending) {
+    if (!c->hostDeferred) {
+      if (cudaMallocHost((void **)&c->hostDeferred, 2 * sizeof(unsigned)) != cudaSuccess) { c->hostDeferred = nullptr; return; }
+      cudaEventCreateWithFlags(&c->evDeferred, cudaEventDisableTiming);
+    }
+    cudaMemcpyAsync(c->hostDeferred, c->cellCursor + 1, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream);
+    cudaMemcpyAsync(c->hostDeferred + 1, c->cellListCount, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream);
+    cudaEventRecord(c->evDeferred, c->stream);
+    c->deferredPending = true;
+  }
 }
 
 void launch_materialize_neighbor_map(sph_ctx *c, float2 *out) {
