@@ -162,7 +162,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch};
+                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -262,6 +262,7 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   if (ok && c->has_pml) {                                                      // :75-76
     A(dalloc(&c->pml, 7 * (size_t)p->num_elastic));
     if (ok) A(cudaMemcpy(c->pml, pml7, 28 * (size_t)p->num_elastic, cudaMemcpyHostToDevice));
+    if (ok) A(dalloc(&c->elasticMask, N));
   }
   if (ok && c->has_elastic) {                                                  // :83-86
     A(dalloc(&c->elastic, (size_t)SPH_NB * p->num_elastic));

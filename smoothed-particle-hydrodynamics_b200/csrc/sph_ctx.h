@@ -47,6 +47,7 @@ struct sph_ctx {
   cudaEvent_t evDeferred;
   bool deferredPending;
   int genericHold;
+  int nbMode;                   // 0 = not decided yet, 1 = tiles, 2 = plain scan (with a probing tile launch every 64 steps)
   bool force_tiled_neighbors;   // SPH_NEIGHBOR_PATH=tiles: the tile kernel whatever the particle count (grid permitting)
   unsigned long long *scanState;  // decoupled look-back tile states
   unsigned *scanTicket;
@@ -54,6 +55,7 @@ struct sph_ctx {
   unsigned epoch;              // step counter for the scan state (no per-step reset needed)
   float2 *nmScratch;           // 32N float2, lazily allocated for sph_read(NEIGHBOR_MAP)
   float4 *readScratch;
+  unsigned *elasticMask;       // N words, scenes with membranes only: bit k = neighbour slot k holds an elastic particle
   bool has_elastic, has_membranes, has_pml;
   bool neighbors_valid;
   bool dispDirty;              // the displacement half of `position` may hold non-zero values (fresh upload)

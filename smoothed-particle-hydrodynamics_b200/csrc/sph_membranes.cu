@@ -56,7 +56,8 @@ __global__ void __launch_bounds__(128) k_membrane_interaction(DevParams d, float
                                                               const uint2 *__restrict__ particleIndex,
                                                               const float *__restrict__ sortedType,
                                                               const int *__restrict__ nb, const int *__restrict__ pml,
-                                                              const int *__restrict__ membraneData) {
+                                                              const int *__restrict__ membraneData,
+                                                              const unsigned *__restrict__ elasticMask) {
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= d.N) return;
   const int src = (int)particleIndex[id].y;
@@ -69,7 +70,12 @@ __global__ void __launch_bounds__(128) k_membrane_interaction(DevParams d, float
     float w_sum = 0.f, w_second = 0.f;
     int jd_counter = 0;
     bool aborted = false;
-    for (int nc = 0; nc < SPH_NB && !aborted; nc++) {
+    // fused path: the integration kernel left a mask of the slots that hold elastic particles, so the (many) liquid
+    // particles without an elastic neighbour skip the scan; the visiting order of the others is unchanged
+    unsigned slots = elasticMask ? elasticMask[id] : 0xffffffffu;
+    while (slots && !aborted) {
+      const int nc = __ffs(slots) - 1;
+      slots &= slots - 1;
       int jd = nb[nb_index(id, nc)];
       if (jd == SPH_NO_ID) break;  // :1557
       if ((int)__ldg(sortedType + jd) != SPH_ELASTIC_PARTICLE) continue;
@@ -150,10 +156,10 @@ void launch_membrane_interaction(sph_ctx *c, bool fuse_finalize) {
   const int *pml = c->has_pml ? c->pml : nullptr;
   if (fuse_finalize)
     k_membrane_interaction<true><<<(c->d.N + 127) / 128, 128, 0, c->stream>>>(c->d, c->position, c->particleIndex,
-                                                                            c->sortedType, c->nbIds, pml, c->membraneData);
+                                                                            c->sortedType, c->nbIds, pml, c->membraneData, c->elasticMask);
   else
     k_membrane_interaction<false><<<(c->d.N + 127) / 128, 128, 0, c->stream>>>(c->d, c->position, c->particleIndex,
-                                                                             c->sortedType, c->nbIds, pml, c->membraneData);
+                                                                             c->sortedType, c->nbIds, pml, c->membraneData, nullptr);
 }
 
 void launch_membrane_finalize(sph_ctx *c) {

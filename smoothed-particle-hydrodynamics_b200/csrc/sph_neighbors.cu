@@ -684,17 +684,27 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   const bool tilesFit = c->d.gx >= 4 && c->d.gy >= 3 && c->d.gz >= 3;
   bool useTiles = tilesFit && !c->force_generic_neighbors && (c->force_tiled_neighbors || c->d.N >= 131072);
   const bool adaptive = useTiles && !c->force_tiled_neighbors;
+  bool wantStats = false, syncStats = false;
   if (adaptive) {
     // The tile kernel pays a fixed price per home block (cell table, staging of 36 cells) and a high one per
     // deferred particle. Scenes with many thinly populated blocks (the worm scene: long box, wall-only cells; 0.25 ms
     // with the plain scan against 0.46 ms) or many overflowing neighbourhoods are faster with the plain scan. Both
-    // paths give identical lists, so switching is free of side effects. Statistics of an earlier step, no sync.
+    // paths give identical lists, so switching has no side effect. The statistics of a tile launch come back
+    // without a sync (except once, after the very first launch) and are acted upon when they arrive.
     if (c->deferredPending && cudaEventQuery(c->evDeferred) == cudaSuccess) {
       c->deferredPending = false;
       const double deferred = (double)c->hostDeferred[0], blocks = (double)c->hostDeferred[1], n = (double)c->d.N;
-      if (deferred > 0.10 * n || n < 64.0 * blocks) c->genericHold = 64;
+      c->nbMode = (deferred > 0.10 * n || n < 64.0 * blocks) ? 2 : 1;
+      if (c->nbMode == 2) c->genericHold = 64;
     }
-    if (c->genericHold > 0) { c->genericHold--; useTiles = false; }
+    if (c->nbMode == 0) {            // first search of this context: tiles, then look at the statistics at once
+      wantStats = syncStats = true;
+    } else if (c->nbMode == 1) {     // tiles suit the fluid: keep watching
+      wantStats = !c->deferredPending;
+    } else {                         // plain scan; every 64 steps one probing tile launch
+      useTiles = false;
+      if (!c->deferredPending && --c->genericHold <= 0) { useTiles = wantStats = true; c->genericHold = 64; }
+    }
   }
   if (!useTiles) {
     int blocks = (c->d.N + 127) / 128;
@@ -706,7 +716,7 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   }
   // persistent CTAs (one resident wave); home blocks handed out through an atomic cursor over cellList
   if (with_density) launch_tiles<true>(c); else launch_tiles<false>(c);
-  if (adaptive && !c->deferredPending) {
+  if (wantStats) {
     if (!c->hostDeferred) {
       if (cudaMallocHost((void **)&c->hostDeferred, 2 * sizeof(unsigned)) != cudaSuccess) { c->hostDeferred = nullptr; return; }
       cudaEventCreateWithFlags(&c->evDeferred, cudaEventDisableTiming);
@@ -715,6 +725,10 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
     cudaMemcpyAsync(c->hostDeferred + 1, c->cellListCount, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream);
     cudaEventRecord(c->evDeferred, c->stream);
     c->deferredPending = true;
+    if (syncStats) {
+      cudaEventSynchronize(c->evDeferred);
+      c->nbMode = 1;  // evaluated by the query at the next call
+    }
   }
 }
 
