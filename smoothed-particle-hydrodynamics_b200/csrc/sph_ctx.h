@@ -48,6 +48,8 @@ struct sph_ctx {
   bool deferredPending;
   int genericHold;
   int nbMode;                   // 0 = not decided yet, 1 = tiles, 2 = plain scan (with a probing tile launch every 64 steps)
+  bool force_list_neighbors;    // SPH_NEIGHBOR_PATH=list: single-sweep hit-list kernel
+  float *soaX, *soaY, *soaZ;    // Npad + 8 each: SoA copy of the sorted positions for the list kernel's 4-wide sweep
   bool force_tiled_neighbors;   // SPH_NEIGHBOR_PATH=tiles: the tile kernel whatever the particle count (grid permitting)
   unsigned long long *scanState;  // decoupled look-back tile states
   unsigned *scanTicket;

@@ -159,6 +159,150 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
   find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
 }
 
+// ---------------------------------------------------------------- list path
+// One thread per particle, like the generic path, but the 8-cell scan is done ONCE:
+//   sweep   four candidates per iteration from SoA copies of the sorted positions (three 128-bit loads), squared
+//           distances in Blackwell's packed fp32x2 pipe, a conservative filter (radius 31h/30 = the largest r_thr the
+//           reference can choose, slightly inflated, FMA allowed) and a branch-free append of (cell k, rank in cell)
+//           to the thread's hit list in shared memory — in scan order, because the thread walks its cells in the
+//           reference's visiting order;
+//   select  the ~35 hits are re-evaluated with the reference's operation order (exact distances from the float4
+//           sorted positions): histogram, r_thr, first 32 within r_thr, rho(t).
+// Nothing inexact reaches the output. A thread whose list overflows (LP_CAP hits, 8191 particles per cell) takes
+// find_neighbors_one. No barriers, full occupancy: the kernel runs at ~90 % issue utilisation.
+#define LP_THREADS 128
+#define LP_CAP 64
+
+__global__ void __launch_bounds__(256) k_soa_positions(int n, const float4 *__restrict__ sp, float *__restrict__ X,
+                                                       float *__restrict__ Y, float *__restrict__ Z) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const float4 p = sp[i];
+    X[i] = p.x; Y[i] = p.y; Z[i] = p.z;
+  } else if (i < n + 8) {  // the sweep reads whole groups of 4: finite padding behind the last particle
+    X[i] = 1.0e30f; Y[i] = 1.0e30f; Z[i] = 1.0e30f;
+  }
+}
+
+template <bool WITH_DENSITY>
+__global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d, const float4 *__restrict__ sp,
+                                                                    const float *__restrict__ X,
+                                                                    const float *__restrict__ Y,
+                                                                    const float *__restrict__ Z,
+                                                                    const unsigned *__restrict__ cellStart,
+                                                                    int *__restrict__ nb, float *__restrict__ rho,
+                                                                    float4 *__restrict__ recA) {
+  __shared__ unsigned short hits[LP_CAP][LP_THREADS];
+  const int tid = threadIdx.x;
+  const int id = blockIdx.x * LP_THREADS + tid;
+  if (id >= d.N) return;
+  const float4 pos = sp[id];
+  const int myCell = (int)pos.w & d.mask;
+  int cells[8];
+  neighbor_cells(d, pos, myCell, cells);
+  int cb[8], ce[8];
+  bool fits = true;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    cb[k] = (int)cellStart[cells[k]];
+    ce[k] = (int)cellStart[cells[k] + 1];
+    fits = fits && (ce[k] - cb[k] < 8192);
+  }
+  const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr (j == 30)
+  const float rfilt2 = rmaxf * rmaxf * 1.0001f;
+  const float2 npx = make_float2(-pos.x, -pos.x), npy = make_float2(-pos.y, -pos.y), npz = make_float2(-pos.z, -pos.z);
+  int n = 0;
+  if (fits) {
+#pragma unroll 1
+    for (int k = 0; k < 8; k++) {
+      const int b = cb[k];
+      const unsigned len = (unsigned)(ce[k] - b);
+      const int enc = (k << 13) - b;  // hit = enc + j = (k << 13) | rank in cell
+#pragma unroll 2
+      for (int j = b & ~3; j < ce[k]; j += 4) {
+        const float4 x4 = __ldg(reinterpret_cast<const float4 *>(X + j));
+        const float4 y4 = __ldg(reinterpret_cast<const float4 *>(Y + j));
+        const float4 z4 = __ldg(reinterpret_cast<const float4 *>(Z + j));
+        const float2 ex0 = __fadd2_rn(make_float2(x4.x, x4.y), npx), ex1 = __fadd2_rn(make_float2(x4.z, x4.w), npx);
+        const float2 ey0 = __fadd2_rn(make_float2(y4.x, y4.y), npy), ey1 = __fadd2_rn(make_float2(y4.z, y4.w), npy);
+        const float2 ez0 = __fadd2_rn(make_float2(z4.x, z4.y), npz), ez1 = __fadd2_rn(make_float2(z4.z, z4.w), npz);
+        const float2 d0 = __ffma2_rn(ez0, ez0, __ffma2_rn(ey0, ey0, __fmul2_rn(ex0, ex0)));
+        const float2 d1 = __ffma2_rn(ez1, ez1, __ffma2_rn(ey1, ey1, __fmul2_rn(ex1, ex1)));
+        // the group is aligned to 4: its ends may reach into the neighbouring cells, masked by the rank test
+        if (d0.x <= rfilt2 && (unsigned)(j - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j); n++; }
+        if (d0.y <= rfilt2 && (unsigned)(j + 1 - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + 1); n++; }
+        if (d1.x <= rfilt2 && (unsigned)(j + 2 - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + 2); n++; }
+        if (d1.y <= rfilt2 && (unsigned)(j + 3 - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + 3); n++; }
+      }
+    }
+  }
+  if (!fits || n > LP_CAP) {
+    find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
+    return;
+  }
+  // exact distances of the hits (the particle itself is among them: skipped by index)
+  auto hit_index = [&](int t) { const unsigned hv = hits[t][tid]; return cb[hv >> 13] + (int)(hv & 8191u); };
+  auto dist2 = [&](int j) {
+    const float4 q = ldg4(sp + j);
+    const float ex = pos.x - q.x, ey = pos.y - q.y, ez = pos.z - q.z;
+    return ex * ex + ey * ey + ez * ez;
+  };
+  unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;  // 30 bins x 6 bits; n <= 64 hits, one is the particle itself
+  const float h2 = d.h * d.h;
+  for (int t = 0; t < n; t++) {
+    const int j = hit_index(t);
+    const float dd = dist2(j);
+    if (j != id && dd <= h2) {
+      float sq;
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
+      int e = min((int)(sq * d.binScale), SPH_RADIUS_SEGMENTS);
+      const int bin = e + ((dd >= d.binT[e + 1]) ? 1 : 0) - ((dd < d.binT[e]) ? 1 : 0);
+      if (bin < SPH_RADIUS_SEGMENTS) {
+        const int w = (bin >= 10 ? 1 : 0) + (bin >= 20 ? 1 : 0);
+        const unsigned long long inc = 1ull << ((bin - 10 * w) * 6);
+        hist0 += (w == 0) ? inc : 0ull;
+        hist1 += (w == 1) ? inc : 0ull;
+        hist2 += (w == 2) ? inc : 0ull;
+      }
+    }
+  }
+  int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
+  {
+    int sum = 0;
+    bool open = true;
+#pragma unroll
+    for (int jj = 0; jj < SPH_RADIUS_SEGMENTS; jj++) {
+      const unsigned long long hw = jj < 10 ? hist0 : (jj < 20 ? hist1 : hist2);
+      sum += (int)((hw >> ((jj % 10) * 6)) & 63ull);
+      if (open && sum >= SPH_NB) { jthr = (sum == SPH_NB) ? jj : jj - 1; open = false; }
+    }
+  }
+  const float r_thr = (float)(jthr + 1) * d.h / SPH_RADIUS_SEGMENTS;
+  const float r2 = r_thr * r_thr;
+  int found = 0;
+  double density = 0.0;
+  for (int t = 0; t < n && found < SPH_NB; t++) {  // first 32 within r_thr, in scan order (:166-174)
+    const int j = hit_index(t);
+    const float dd = dist2(j);
+    if (j != id && dd <= r2) {
+      nb[nb_index(id, found)] = j;
+      if (WITH_DENSITY) {  // pcisph_computeDensity term, sphFluid.cl:505-507
+        const float r = sqrtf(dd) * d.simScale;
+        const float rr = r * r;
+        density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
+      }
+      found++;
+    }
+  }
+  for (int k = found; k < SPH_NB; k++) nb[nb_index(id, k)] = SPH_NO_ID;
+  if (WITH_DENSITY) {  // sphFluid.cl:514-517
+    if (density < (double)d.hScaled6) density = (double)d.hScaled6;
+    density *= d.massWpoly6;
+    rho[id] = (float)density;
+    if (recA) reinterpret_cast<float *>(recA)[8 * (size_t)id + 7] = (float)density;
+  }
+}
+
 // ---------------------------------------------------------------- tiled path (the product path)
 // One persistent kernel, k_neighbor_tiles. A CTA takes a HOME BLOCK = the two hash cells (2b, 2b+1),
 // whose particles are one contiguous range of the sorted arrays, and
@@ -682,7 +826,7 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   // Below ~1000 home blocks (two per resident CTA) its persistent CTAs do not balance and the plain scan wins
   // (config A, 61 k particles: 0.17 ms against 0.32 ms).
   const bool tilesFit = c->d.gx >= 4 && c->d.gy >= 3 && c->d.gz >= 3;
-  bool useTiles = tilesFit && !c->force_generic_neighbors && (c->force_tiled_neighbors || c->d.N >= 131072);
+  bool useTiles = tilesFit && !c->force_generic_neighbors && !c->force_list_neighbors && (c->force_tiled_neighbors || c->d.N >= 131072);
   const bool adaptive = useTiles && !c->force_tiled_neighbors;
   bool wantStats = false, syncStats = false;
   if (adaptive) {
@@ -705,6 +849,18 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
       useTiles = false;
       if (!c->deferredPending && --c->genericHold <= 0) { useTiles = wantStats = true; c->genericHold = 64; }
     }
+  }
+  if (!useTiles && !c->force_generic_neighbors) {
+    const int n = c->d.N;
+    k_soa_positions<<<(n + 8 + 255) / 256, 256, 0, c->stream>>>(n, c->sortedPosition, c->soaX, c->soaY, c->soaZ);
+    const int blocks = (n + LP_THREADS - 1) / LP_THREADS;
+    if (with_density)
+      k_find_neighbors_list<true><<<blocks, LP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soaX, c->soaY, c->soaZ,
+                                                                       c->cellStart, c->nbIds, c->rho, c->recA);
+    else
+      k_find_neighbors_list<false><<<blocks, LP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soaX, c->soaY, c->soaZ,
+                                                                        c->cellStart, c->nbIds, c->rho, nullptr);
+    return;
   }
   if (!useTiles) {
     int blocks = (c->d.N + 127) / 128;

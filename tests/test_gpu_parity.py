@@ -38,7 +38,7 @@ STAGE_OUTPUTS = {
 }
 
 
-@pytest.fixture(scope="module", autouse=True, params=["tiles", "generic"])
+@pytest.fixture(scope="module", autouse=True, params=["tiles", "generic", "list"])
 def neighbor_path(request):
     """Every parity test runs twice: with the tile kernel forced (the path large fluids take; the test scenes are
     below the size where the library picks it by itself) and with the one-thread-per-particle scan."""
