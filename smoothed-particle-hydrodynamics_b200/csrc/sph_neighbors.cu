@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 
 // ---------------------------------------------------------------- list path
 // One thread per particle, like the generic path, but the 8-cell scan is done ONCE:
-//   sweep   four candidates per iteration from SoA copies of the sorted positions (three 128-bit loads), squared
+//   sweep   eight candidates per iteration from SoA copies of the sorted positions (three 256-bit loads), squared
 //           distances in Blackwell's packed fp32x2 pipe, a conservative filter (radius 31h/30 = the largest r_thr the
 //           reference can choose, slightly inflated, FMA allowed) and a branch-free append of (cell k, rank in cell)
 //           to the thread's hit list in shared memory — in scan order, because the thread walks its cells in the
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(256) k_soa_positions(int n, const float4 *__re
   if (i < n) {
     const float4 p = sp[i];
     X[i] = p.x; Y[i] = p.y; Z[i] = p.z;
-  } else if (i < n + 8) {  // the sweep reads whole groups of 4: finite padding behind the last particle
+  } else if (i < n + 8) {  // the sweep reads whole groups of 8: finite padding behind the last particle
     X[i] = 1.0e30f; Y[i] = 1.0e30f; Z[i] = 1.0e30f;
   }
 }
@@ -193,8 +193,37 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
                                                                     int *__restrict__ nb, float *__restrict__ rho,
                                                                     float4 *__restrict__ recA) {
   __shared__ unsigned short hits[LP_CAP][LP_THREADS];
+  __shared__ int keyOf[LP_THREADS];
+  __shared__ unsigned char srcOf[LP_THREADS];
   const int tid = threadIdx.x;
-  const int id = blockIdx.x * LP_THREADS + tid;
+  // Lanes that share (cell, octant) walk the same cells in lockstep and load the same addresses. The CTA's 128
+  // consecutive particles (about two cells) are therefore dealt to the threads in (cell, octant) order — a rank by
+  // counting over the keys in shared memory.
+  int id;
+  {
+    const int mine = blockIdx.x * LP_THREADS + tid;
+    int key = 0x7fffffff;  // beyond N: sorts last
+    if (mine < d.N) {
+      const float4 p = sp[mine];
+      const float cfx = (float)(int)(p.x * d.cellSizeInv) * d.cellSize;
+      const float cfy = (float)(int)(p.y * d.cellSizeInv) * d.cellSize;
+      const float cfz = (float)(int)(p.z * d.cellSizeInv) * d.cellSize;
+      const int oct = ((((p.x - d.xmin) - cfx) < d.h) ? 0 : 1) | ((((p.y - d.ymin) - cfy) < d.h) ? 0 : 2) |
+                      ((((p.z - d.zmin) - cfz) < d.h) ? 0 : 4);
+      key = ((((int)p.w & d.mask) & 0x0fffffff) << 3) | oct;
+    }
+    keyOf[tid] = key;
+    __syncthreads();
+    int rank = 0;
+#pragma unroll 8
+    for (int t = 0; t < LP_THREADS; t++) {
+      const int kt = keyOf[t];
+      rank += (kt < key || (kt == key && t < tid)) ? 1 : 0;
+    }
+    srcOf[rank] = (unsigned char)tid;
+    __syncthreads();
+    id = blockIdx.x * LP_THREADS + (int)srcOf[tid];
+  }
   if (id >= d.N) return;
   const float4 pos = sp[id];
   const int myCell = (int)pos.w & d.mask;
@@ -218,21 +247,25 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
       const int b = cb[k];
       const unsigned len = (unsigned)(ce[k] - b);
       const int enc = (k << 13) - b;  // hit = enc + j = (k << 13) | rank in cell
-#pragma unroll 2
-      for (int j = b & ~3; j < ce[k]; j += 4) {
-        const float4 x4 = __ldg(reinterpret_cast<const float4 *>(X + j));
-        const float4 y4 = __ldg(reinterpret_cast<const float4 *>(Y + j));
-        const float4 z4 = __ldg(reinterpret_cast<const float4 *>(Z + j));
-        const float2 ex0 = __fadd2_rn(make_float2(x4.x, x4.y), npx), ex1 = __fadd2_rn(make_float2(x4.z, x4.w), npx);
-        const float2 ey0 = __fadd2_rn(make_float2(y4.x, y4.y), npy), ey1 = __fadd2_rn(make_float2(y4.z, y4.w), npy);
-        const float2 ez0 = __fadd2_rn(make_float2(z4.x, z4.y), npz), ez1 = __fadd2_rn(make_float2(z4.z, z4.w), npz);
-        const float2 d0 = __ffma2_rn(ez0, ez0, __ffma2_rn(ey0, ey0, __fmul2_rn(ex0, ex0)));
-        const float2 d1 = __ffma2_rn(ez1, ez1, __ffma2_rn(ey1, ey1, __fmul2_rn(ex1, ex1)));
-        // the group is aligned to 4: its ends may reach into the neighbouring cells, masked by the rank test
-        if (d0.x <= rfilt2 && (unsigned)(j - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j); n++; }
-        if (d0.y <= rfilt2 && (unsigned)(j + 1 - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + 1); n++; }
-        if (d1.x <= rfilt2 && (unsigned)(j + 2 - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + 2); n++; }
-        if (d1.y <= rfilt2 && (unsigned)(j + 3 - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + 3); n++; }
+#pragma unroll 1
+      for (int j = b & ~7; j < ce[k]; j += 8) {  // 8 candidates per pass: three 256-bit loads
+        float4 xa, xb, ya, yb, za, zb;
+        ld256(reinterpret_cast<const float4 *>(X + j), xa, xb);
+        ld256(reinterpret_cast<const float4 *>(Y + j), ya, yb);
+        ld256(reinterpret_cast<const float4 *>(Z + j), za, zb);
+        auto pair = [&](float x0, float x1, float y0, float y1, float z0, float z1) {
+          const float2 ex = __fadd2_rn(make_float2(x0, x1), npx), ey = __fadd2_rn(make_float2(y0, y1), npy),
+                       ez = __fadd2_rn(make_float2(z0, z1), npz);
+          return __ffma2_rn(ez, ez, __ffma2_rn(ey, ey, __fmul2_rn(ex, ex)));
+        };
+        const float2 d0 = pair(xa.x, xa.y, ya.x, ya.y, za.x, za.y), d1 = pair(xa.z, xa.w, ya.z, ya.w, za.z, za.w);
+        const float2 d2 = pair(xb.x, xb.y, yb.x, yb.y, zb.x, zb.y), d3 = pair(xb.z, xb.w, yb.z, yb.w, zb.z, zb.w);
+        // the group is aligned to 8: its ends may reach into the neighbouring cells, masked by the rank test
+        auto keep = [&](float dd, int i) {
+          if (dd <= rfilt2 && (unsigned)(j + i - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + i); n++; }
+        };
+        keep(d0.x, 0); keep(d0.y, 1); keep(d1.x, 2); keep(d1.y, 3);
+        keep(d2.x, 4); keep(d2.y, 5); keep(d3.x, 6); keep(d3.y, 7);
       }
     }
   }
@@ -249,10 +282,27 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
   };
   unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;  // 30 bins x 6 bits; n <= 64 hits, one is the particle itself
   const float h2 = d.h * d.h;
+  int found = 0;
+  double density = 0.0;
+  auto take = [&](int j, float dd) {  // :166-174 + the pcisph_computeDensity term, sphFluid.cl:505-507
+    nb[nb_index(id, found)] = j;
+    if (WITH_DENSITY) {
+      const float r = sqrtf(dd) * d.simScale;
+      const float rr = r * r;
+      density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
+    }
+    found++;
+  };
+  // One pass builds the histogram AND selects as if the histogram left r_thr at its largest value (fewer than 32
+  // candidates within h: the usual case at rest density). Only the other particles repeat the selection with their
+  // smaller r_thr: the exact distances are gathered once for most lanes.
+  const float r2open = ((float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS) *
+                       ((float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS);
   for (int t = 0; t < n; t++) {
     const int j = hit_index(t);
+    if (j == id) continue;
     const float dd = dist2(j);
-    if (j != id && dd <= h2) {
+    if (dd <= h2) {
       float sq;
       asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
       int e = min((int)(sq * d.binScale), SPH_RADIUS_SEGMENTS);
@@ -265,6 +315,7 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
         hist2 += (w == 2) ? inc : 0ull;
       }
     }
+    if (dd <= r2open && found < SPH_NB) take(j, dd);
   }
   int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
   {
@@ -277,21 +328,16 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
       if (open && sum >= SPH_NB) { jthr = (sum == SPH_NB) ? jj : jj - 1; open = false; }
     }
   }
-  const float r_thr = (float)(jthr + 1) * d.h / SPH_RADIUS_SEGMENTS;
-  const float r2 = r_thr * r_thr;
-  int found = 0;
-  double density = 0.0;
-  for (int t = 0; t < n && found < SPH_NB; t++) {  // first 32 within r_thr, in scan order (:166-174)
-    const int j = hit_index(t);
-    const float dd = dist2(j);
-    if (j != id && dd <= r2) {
-      nb[nb_index(id, found)] = j;
-      if (WITH_DENSITY) {  // pcisph_computeDensity term, sphFluid.cl:505-507
-        const float r = sqrtf(dd) * d.simScale;
-        const float rr = r * r;
-        density += (double)((d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr));
-      }
-      found++;
+  if (jthr != SPH_RADIUS_SEGMENTS) {  // a smaller r_thr: select again
+    const float r_thr = (float)(jthr + 1) * d.h / SPH_RADIUS_SEGMENTS;
+    const float r2 = r_thr * r_thr;
+    found = 0;
+    density = 0.0;
+    for (int t = 0; t < n && found < SPH_NB; t++) {
+      const int j = hit_index(t);
+      if (j == id) continue;
+      const float dd = dist2(j);
+      if (dd <= r2) take(j, dd);
     }
   }
   for (int k = found; k < SPH_NB; k++) nb[nb_index(id, k)] = SPH_NO_ID;
