@@ -162,7 +162,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soaX, c->soaY, c->soaZ};
+                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soa};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -222,6 +222,9 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
     c->force_generic_neighbors = (e && e[0] == '1') || (q && !strcmp(q, "generic"));
     c->force_tiled_neighbors = q && !strcmp(q, "tiles");
     c->force_list_neighbors = q && !strcmp(q, "list");
+    c->auto_tiles = q && !strcmp(q, "auto");
+    const char *lv = getenv("SPH_LIST_VARIANT");
+    c->list_variant = lv ? atoi(lv) : 2;
   }
   bool ok = true;
 #define A(x) ok = ok && ((e = (x)) == cudaSuccess)
@@ -241,9 +244,7 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->acceleration, 2 * N));
   A(dalloc(&c->muscle, (size_t)p->muscle_count));
   A(dalloc(&c->nbIds, Npad * SPH_NB));
-  A(dalloc(&c->soaX, Npad + 8));
-  A(dalloc(&c->soaY, Npad + 8));
-  A(dalloc(&c->soaZ, Npad + 8));
+  A(dalloc(&c->soa, 3 * (Npad + 32)));
   A(dalloc(&c->cellCount, G + 2));
   A(dalloc(&c->key, N));
   A(dalloc(&c->tmpSerial, N));

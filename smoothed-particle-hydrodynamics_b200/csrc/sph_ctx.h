@@ -49,7 +49,9 @@ struct sph_ctx {
   int genericHold;
   int nbMode;                   // 0 = not decided yet, 1 = tiles, 2 = plain scan (with a probing tile launch every 64 steps)
   bool force_list_neighbors;    // SPH_NEIGHBOR_PATH=list: single-sweep hit-list kernel
-  float *soaX, *soaY, *soaZ;    // Npad + 8 each: SoA copy of the sorted positions for the list kernel's 4-wide sweep
+  bool auto_tiles;               // SPH_NEIGHBOR_PATH=auto: the round-1 policy (tiles for large fluids, watched by the statistics)
+  int list_variant;             // SPH_LIST_VARIANT: sweep variant of the list kernel (experiments)
+  float *soa;                   // 3 (Npad + 32): sweep copy of the sorted positions, groups of 8 as x[8] | y[8] | z[8] (k_soa_positions)
   bool force_tiled_neighbors;   // SPH_NEIGHBOR_PATH=tiles: the tile kernel whatever the particle count (grid permitting)
   unsigned long long *scanState;  // decoupled look-back tile states
   unsigned *scanTicket;

@@ -10,6 +10,8 @@
 // float2 (id, distance) layout is materialised on demand: distance = sqrtf(dx²+dy²+dz²)*scale
 // recomputed from sortedPosition is bit-identical to the value findNeighbors stored
 // (same operands, same operation order, sphFluid.cl:154-171).
+#include <cuda_fp16.h>
+
 #include "sph_ctx.h"
 
 __global__ void __launch_bounds__(256) k_clear_neighbors(int *__restrict__ nb, size_t n) {
@@ -173,36 +175,68 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #define LP_THREADS 128
 #define LP_CAP 64
 
-__global__ void __launch_bounds__(256) k_soa_positions(int n, const float4 *__restrict__ sp, float *__restrict__ X,
-                                                       float *__restrict__ Y, float *__restrict__ Z) {
+// Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
+// 256-bit loads of a sweep pass share one address computation.
+__global__ void __launch_bounds__(256) k_soa_positions(int n, const float4 *__restrict__ sp, float *__restrict__ S) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  float *o = S + 24 * (size_t)(i >> 3) + (i & 7);
   if (i < n) {
     const float4 p = sp[i];
-    X[i] = p.x; Y[i] = p.y; Z[i] = p.z;
-  } else if (i < n + 8) {  // the sweep reads whole groups of 8: finite padding behind the last particle
-    X[i] = 1.0e30f; Y[i] = 1.0e30f; Z[i] = 1.0e30f;
+    o[0] = p.x; o[8] = p.y; o[16] = p.z;
+  } else if (i < n + 16) {  // the sweep reads whole groups of 8: finite padding behind the last particle
+    o[0] = 1.0e30f; o[8] = 1.0e30f; o[16] = 1.0e30f;
   }
 }
 
-template <bool WITH_DENSITY>
+// Half-precision sweep copy (list kernel, VAR 2): cell-LOCAL coordinates in units of h, u = (p - cell corner) / h in
+// [0, 2], where the cell corner is the one the hash uses (cx = (int)(p.x * cellSizeInv), sphFluid.cl:197-199). Groups
+// of 16 particles as x[16] | y[16] | z[16] = 96 bytes; inside a 16-vector, half2 register r holds particles (r, r + 8)
+// so that the sign bits of the packed distances land in ascending particle order (bits 0-7 and 16-23).
+#define LP_HPAD 100.0f   // padding coordinate: far from everything, its square still finite in half precision
+__device__ __forceinline__ float3 cell_local_h(const DevParams &d, const float4 p, const float hInv) {
+  const float lx = p.x - (float)(int)(p.x * d.cellSizeInv) * d.cellSize;
+  const float ly = p.y - (float)(int)(p.y * d.cellSizeInv) * d.cellSize;
+  const float lz = p.z - (float)(int)(p.z * d.cellSizeInv) * d.cellSize;
+  return make_float3(lx * hInv, ly * hInv, lz * hInv);
+}
+__global__ void __launch_bounds__(256) k_soa_positions_half(DevParams d, const float4 *__restrict__ sp,
+                                                            __half *__restrict__ S) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int s = i & 15;
+  __half *o = S + 48 * (size_t)(i >> 4) + 2 * (s & 7) + (s >> 3);
+  if (i < d.N) {
+    const float3 u = cell_local_h(d, sp[i], 1.0f / d.h);
+    o[0] = __float2half_rn(u.x); o[16] = __float2half_rn(u.y); o[32] = __float2half_rn(u.z);
+  } else if (i < d.N + 32) {  // the sweep reads whole groups of 16
+    o[0] = __float2half_rn(LP_HPAD); o[16] = __float2half_rn(LP_HPAD); o[32] = __float2half_rn(LP_HPAD);
+  }
+}
+
+__device__ __forceinline__ void ld256u(const void *p, uint4 &a, uint4 &b) {
+  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+               : "l"(p));
+}
+
+template <bool WITH_DENSITY, int VAR>
 __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d, const float4 *__restrict__ sp,
-                                                                    const float *__restrict__ X,
-                                                                    const float *__restrict__ Y,
-                                                                    const float *__restrict__ Z,
+                                                                    const float *__restrict__ S,
                                                                     const unsigned *__restrict__ cellStart,
                                                                     int *__restrict__ nb, float *__restrict__ rho,
                                                                     float4 *__restrict__ recA) {
-  __shared__ unsigned short hits[LP_CAP][LP_THREADS];
-  __shared__ int keyOf[LP_THREADS];
+  __shared__ unsigned short hits[LP_CAP + 1][LP_THREADS];
+  __shared__ int binCount[64], binBase[64];
+  __shared__ int binTot0;
   __shared__ unsigned char srcOf[LP_THREADS];
   const int tid = threadIdx.x;
   // Lanes that share (cell, octant) walk the same cells in lockstep and load the same addresses. The CTA's 128
-  // consecutive particles (about two cells) are therefore dealt to the threads in (cell, octant) order — a rank by
-  // counting over the keys in shared memory.
+  // consecutive particles (about two cells) are therefore dealt to the threads grouped by (cell, octant): a counting
+  // sort over 8 cells x 8 octants in shared memory (cells beyond the eighth share the last bins; the order inside
+  // a bin is arbitrary — grouping only affects speed, every thread still handles exactly one particle).
   int id;
   {
-    const int mine = blockIdx.x * LP_THREADS + tid;
-    int key = 0x7fffffff;  // beyond N: sorts last
+    const int first = blockIdx.x * LP_THREADS, mine = first + tid;
+    int bin = 63;  // beyond N
     if (mine < d.N) {
       const float4 p = sp[mine];
       const float cfx = (float)(int)(p.x * d.cellSizeInv) * d.cellSize;
@@ -210,19 +244,28 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
       const float cfz = (float)(int)(p.z * d.cellSizeInv) * d.cellSize;
       const int oct = ((((p.x - d.xmin) - cfx) < d.h) ? 0 : 1) | ((((p.y - d.ymin) - cfy) < d.h) ? 0 : 2) |
                       ((((p.z - d.zmin) - cfz) < d.h) ? 0 : 4);
-      key = ((((int)p.w & d.mask) & 0x0fffffff) << 3) | oct;
+      const int c0 = (int)sp[first].w & d.mask;  // sorted order: cell ids ascend inside the CTA
+      bin = (min(max(((int)p.w & d.mask) - c0, 0), 7) << 3) | oct;
     }
-    keyOf[tid] = key;
+    if (tid < 64) binCount[tid] = 0;
     __syncthreads();
-    int rank = 0;
-#pragma unroll 8
-    for (int t = 0; t < LP_THREADS; t++) {
-      const int kt = keyOf[t];
-      rank += (kt < key || (kt == key && t < tid)) ? 1 : 0;
+    const int slot = atomicAdd(&binCount[bin], 1);
+    __syncthreads();
+    if (tid < 64) {
+      const int c = binCount[tid];
+      int inc = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, inc, o);
+        if ((tid & 31) >= o) inc += u;
+      }
+      binBase[tid] = inc - c;
+      if (tid == 31) binTot0 = inc;
     }
-    srcOf[rank] = (unsigned char)tid;
     __syncthreads();
-    id = blockIdx.x * LP_THREADS + (int)srcOf[tid];
+    srcOf[binBase[bin] + (bin >= 32 ? binTot0 : 0) + slot] = (unsigned char)tid;
+    __syncthreads();
+    id = first + (int)srcOf[tid];
   }
   if (id >= d.N) return;
   const float4 pos = sp[id];
@@ -241,7 +284,98 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
   const float rfilt2 = rmaxf * rmaxf * 1.0001f;
   const float2 npx = make_float2(-pos.x, -pos.x), npy = make_float2(-pos.y, -pos.y), npz = make_float2(-pos.z, -pos.z);
   int n = 0;
-  if (fits) {
+  if (fits && VAR == 2) {
+    // half-precision variant: 16 candidates per pass from the cell-local fp16 copy (three 256-bit loads = half the
+    // bytes per candidate through the L1 data pipe, which bounds the fp32 sweep). The home particle is expressed in
+    // the visited cell's frame: u_p - 2 (kx sx, ky sy, kz sz). Everything is in units of h; the filter constant
+    // covers the largest r_thr, (31/30)^2 * 1.0001 = 1.0679, plus the worst-case fp16 error of a true hit
+    // (coordinates 0.002 per axis -> 0.007 on d2, three fma roundings 0.0015): T = 1 + 92/1024 = 1.0898.
+    const float3 up = cell_local_h(d, pos, 1.0f / d.h);
+    const float sgx = (((pos.x - d.xmin) - (float)(int)(pos.x * d.cellSizeInv) * d.cellSize) < d.h) ? -2.0f : 2.0f;
+    const float sgy = (((pos.y - d.ymin) - (float)(int)(pos.y * d.cellSizeInv) * d.cellSize) < d.h) ? -2.0f : 2.0f;
+    const float sgz = (((pos.z - d.zmin) - (float)(int)(pos.z * d.cellSizeInv) * d.cellSize) < d.h) ? -2.0f : 2.0f;
+    const __half2 nT = __float2half2_rn(-1.08984375f);
+    const __half *Sh = reinterpret_cast<const __half *>(S);
+    int nh = 0;
+#pragma unroll 1
+    for (int k = 0; k < 8; k++) {
+      const int b = cb[k], e = ce[k];
+      const int enc = (k << 13) - b - 1;  // hit = enc + j + candidate + 1 = (k << 13) | rank in cell
+      const __half2 px = __float2half2_rn(up.x - (((0xB2 >> k) & 1) ? sgx : 0.0f));
+      const __half2 py = __float2half2_rn(up.y - (((0xD4 >> k) & 1) ? sgy : 0.0f));
+      const __half2 pz = __float2half2_rn(up.z - (((0xE8 >> k) & 1) ? sgz : 0.0f));
+#pragma unroll 1
+      for (int j = b & ~15; j < e; j += 16) {
+        uint4 xa, xb, ya, yb, za, zb;
+        const __half *g = Sh + 3 * (size_t)j;
+        ld256u(g, xa, xb);
+        ld256u(g + 16, ya, yb);
+        ld256u(g + 32, za, zb);
+        unsigned m = 0u;  // bit r = candidate j + r, bit 16 + r = candidate j + 8 + r (r < 8): inside the filter
+        auto lane2 = [&](unsigned x, unsigned y, unsigned z, int r) {
+          const __half2 ex = __hsub2(*reinterpret_cast<const __half2 *>(&x), px);
+          const __half2 ey = __hsub2(*reinterpret_cast<const __half2 *>(&y), py);
+          const __half2 ez = __hsub2(*reinterpret_cast<const __half2 *>(&z), pz);
+          const __half2 a = __hfma2(ez, ez, __hfma2(ey, ey, __hfma2(ex, ex, nT)));  // d2 - T: negative = hit
+          m |= ((*reinterpret_cast<const unsigned *>(&a)) >> (15 - r)) & (0x00010001u << r);
+        };
+        lane2(xa.x, ya.x, za.x, 0); lane2(xa.y, ya.y, za.y, 1); lane2(xa.z, ya.z, za.z, 2); lane2(xa.w, ya.w, za.w, 3);
+        lane2(xb.x, yb.x, zb.x, 4); lane2(xb.y, yb.y, zb.y, 5); lane2(xb.z, yb.z, zb.z, 6); lane2(xb.w, yb.w, zb.w, 7);
+        // the group is aligned to 16: its ends may reach into the neighbouring cells
+        const unsigned vm = (0xffffu << max(b - j, 0)) & (0xffffu >> max(j + 16 - e, 0));
+        m &= (vm & 0xffu) | ((vm & 0xff00u) << 8);
+        const int v0 = enc + j;
+        while (m) {
+          const int i = __ffs(m);  // 1-based bit; bits 17..24 are candidates 9..16 (1-based)
+          m &= m - 1u;
+          hits[min(nh, LP_CAP)][tid] = (unsigned short)(v0 + i - ((i > 16) ? 8 : 0));  // row LP_CAP = overflow, never read
+          nh++;
+        }
+      }
+    }
+    n = nh;
+  } else if (fits && VAR == 1) {
+    // branch-free variant: the sign bits of (d2 - filter radius^2) are funnel-shifted into an 8-bit mask, the slots
+    // of the aligned group that lie outside the cell are masked off, and the (rare) hits are appended by a loop over
+    // the set bits
+    const float2 nr2 = make_float2(-rfilt2, -rfilt2);
+    int nh = 0;
+#pragma unroll 1
+    for (int k = 0; k < 8; k++) {
+      const int b = cb[k], e = ce[k];
+      const int enc = (k << 13) - b - 1;  // hit = enc + j + ffs = (k << 13) | rank in cell
+#pragma unroll 1
+      for (int j = b & ~7; j < e; j += 8) {  // 8 candidates per pass: three 256-bit loads
+        float4 xa, xb, ya, yb, za, zb;
+        const float4 *g = reinterpret_cast<const float4 *>(S + 3 * (size_t)j);
+        ld256(g, xa, xb);
+        ld256(g + 2, ya, yb);
+        ld256(g + 4, za, zb);
+        auto pair = [&](float x0, float x1, float y0, float y1, float z0, float z1) {
+          const float2 ex = __fadd2_rn(make_float2(x0, x1), npx), ey = __fadd2_rn(make_float2(y0, y1), npy),
+                       ez = __fadd2_rn(make_float2(z0, z1), npz);
+          return __fadd2_rn(__ffma2_rn(ez, ez, __ffma2_rn(ey, ey, __fmul2_rn(ex, ex))), nr2);  // < 0: inside the filter
+        };
+        const float2 d0 = pair(xa.x, xa.y, ya.x, ya.y, za.x, za.y), d1 = pair(xa.z, xa.w, ya.z, ya.w, za.z, za.w);
+        const float2 d2 = pair(xb.x, xb.y, yb.x, yb.y, zb.x, zb.y), d3 = pair(xb.z, xb.w, yb.z, yb.w, zb.z, zb.w);
+        unsigned m = 0u;  // bit i = candidate j + i inside the filter radius
+        m = __funnelshift_l(__float_as_uint(d3.y), m, 1); m = __funnelshift_l(__float_as_uint(d3.x), m, 1);
+        m = __funnelshift_l(__float_as_uint(d2.y), m, 1); m = __funnelshift_l(__float_as_uint(d2.x), m, 1);
+        m = __funnelshift_l(__float_as_uint(d1.y), m, 1); m = __funnelshift_l(__float_as_uint(d1.x), m, 1);
+        m = __funnelshift_l(__float_as_uint(d0.y), m, 1); m = __funnelshift_l(__float_as_uint(d0.x), m, 1);
+        // the group is aligned to 8: its ends may reach into the neighbouring cells
+        m &= (0xffu << max(b - j, 0)) & (0xffu >> max(j + 8 - e, 0));
+        const int v0 = enc + j;
+        while (m) {
+          const int i = __ffs(m);
+          m &= m - 1u;
+          hits[min(nh, LP_CAP)][tid] = (unsigned short)(v0 + i);  // row LP_CAP = overflow, never read
+          nh++;
+        }
+      }
+    }
+    n = nh;
+  } else if (fits) {
 #pragma unroll 1
     for (int k = 0; k < 8; k++) {
       const int b = cb[k];
@@ -250,9 +384,10 @@ __global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d,
 #pragma unroll 1
       for (int j = b & ~7; j < ce[k]; j += 8) {  // 8 candidates per pass: three 256-bit loads
         float4 xa, xb, ya, yb, za, zb;
-        ld256(reinterpret_cast<const float4 *>(X + j), xa, xb);
-        ld256(reinterpret_cast<const float4 *>(Y + j), ya, yb);
-        ld256(reinterpret_cast<const float4 *>(Z + j), za, zb);
+        const float4 *g = reinterpret_cast<const float4 *>(S + 3 * (size_t)j);
+        ld256(g, xa, xb);
+        ld256(g + 2, ya, yb);
+        ld256(g + 4, za, zb);
         auto pair = [&](float x0, float x1, float y0, float y1, float z0, float z1) {
           const float2 ex = __fadd2_rn(make_float2(x0, x1), npx), ey = __fadd2_rn(make_float2(y0, y1), npy),
                        ez = __fadd2_rn(make_float2(z0, z1), npz);
@@ -872,7 +1007,7 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   // Below ~1000 home blocks (two per resident CTA) its persistent CTAs do not balance and the plain scan wins
   // (config A, 61 k particles: 0.17 ms against 0.32 ms).
   const bool tilesFit = c->d.gx >= 4 && c->d.gy >= 3 && c->d.gz >= 3;
-  bool useTiles = tilesFit && !c->force_generic_neighbors && !c->force_list_neighbors && (c->force_tiled_neighbors || c->d.N >= 131072);
+  bool useTiles = tilesFit && !c->force_generic_neighbors && !c->force_list_neighbors && (c->force_tiled_neighbors || (c->auto_tiles && c->d.N >= 131072));
   const bool adaptive = useTiles && !c->force_tiled_neighbors;
   bool wantStats = false, syncStats = false;
   if (adaptive) {
@@ -898,14 +1033,24 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   }
   if (!useTiles && !c->force_generic_neighbors) {
     const int n = c->d.N;
-    k_soa_positions<<<(n + 8 + 255) / 256, 256, 0, c->stream>>>(n, c->sortedPosition, c->soaX, c->soaY, c->soaZ);
-    const int blocks = (n + LP_THREADS - 1) / LP_THREADS;
-    if (with_density)
-      k_find_neighbors_list<true><<<blocks, LP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soaX, c->soaY, c->soaZ,
-                                                                       c->cellStart, c->nbIds, c->rho, c->recA);
+    // the half-precision sweep assumes that a true neighbour found in visited cell k sits in the cell at spatial
+    // offset (kx sx, ky sy, kz sz): true when no other offset in {-2..2}^3 maps to the same (masked, wrapped) id
+    const long long span = 2 + 2 * (long long)c->d.gx + 2 * (long long)c->d.gx * c->d.gy;
+    const bool halfOk = c->d.gx >= 4 && c->d.gy >= 4 && c->d.gz >= 4 && span < (long long)c->d.G &&
+                        span < (long long)c->d.mask + 1;
+    const int var = (c->list_variant == 2 && !halfOk) ? 1 : c->list_variant;
+    if (var == 2)
+      k_soa_positions_half<<<(n + 32 + 255) / 256, 256, 0, c->stream>>>(c->d, c->sortedPosition, reinterpret_cast<__half *>(c->soa));
     else
-      k_find_neighbors_list<false><<<blocks, LP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soaX, c->soaY, c->soaZ,
-                                                                        c->cellStart, c->nbIds, c->rho, nullptr);
+      k_soa_positions<<<(n + 16 + 255) / 256, 256, 0, c->stream>>>(n, c->sortedPosition, c->soa);
+    const int blocks = (n + LP_THREADS - 1) / LP_THREADS;
+#define LP_LAUNCH(WD, V, REC)                                                                                      \
+  k_find_neighbors_list<WD, V><<<blocks, LP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, \
+                                                                     c->rho, REC)
+    if (var == 0) { if (with_density) LP_LAUNCH(true, 0, c->recA); else LP_LAUNCH(false, 0, nullptr); }
+    else if (var == 1) { if (with_density) LP_LAUNCH(true, 1, c->recA); else LP_LAUNCH(false, 1, nullptr); }
+    else { if (with_density) LP_LAUNCH(true, 2, c->recA); else LP_LAUNCH(false, 2, nullptr); }
+#undef LP_LAUNCH
     return;
   }
   if (!useTiles) {

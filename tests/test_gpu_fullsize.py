@@ -46,7 +46,7 @@ def with_path(path):
 def test_fluid_256k_two_steps_against_oracle(P):
     O = common.oracle_lib()
     p, pos, vel = workload(P, "fluid_256k")
-    old = with_path(None)   # the library's own choice: tiles at this size
+    old = with_path(None)   # the library's own choice: the list kernel
     try:
         a, b = P.create(p, pos, vel), O.create(p, pos, vel)
         for step in range(2):
@@ -101,7 +101,7 @@ def test_fluid_8m_tile_kernel_equals_plain_scan(P):
     out = {}
     old = os.environ.get("SPH_NEIGHBOR_PATH")
     try:
-        for path in ("tiles", "generic"):
+        for path in ("tiles", "generic", "list"):
             with_path(path)
             ctx = P.create(p, pos, vel)
             ctx.step()
@@ -110,8 +110,9 @@ def test_fluid_8m_tile_kernel_equals_plain_scan(P):
             ctx.close()
     finally:
         with_path(old)
-    assert common.first_mismatch(out["tiles"][0], out["generic"][0]) is None
-    assert common.first_mismatch(out["tiles"][1], out["generic"][1]) is None
+    for path in ("tiles", "list"):
+        assert common.first_mismatch(out[path][0], out["generic"][0]) is None
+        assert common.first_mismatch(out[path][1], out["generic"][1]) is None
     assert not np.array_equal(out["tiles"][0], pos), "the fluid did not move"
 
 
@@ -129,7 +130,7 @@ def test_dambreak_1m_moving_fluid_tile_kernel_equals_plain_scan(P):
     out = {}
     old = os.environ.get("SPH_NEIGHBOR_PATH")
     try:
-        for path in ("tiles", "generic"):
+        for path in ("tiles", "generic", "list"):
             with_path(path)
             ctx = P.create(p, pos, vel)
             for _ in range(40):
@@ -139,8 +140,9 @@ def test_dambreak_1m_moving_fluid_tile_kernel_equals_plain_scan(P):
             ctx.close()
     finally:
         with_path(old)
-    for a, b, name in zip(out["tiles"], out["generic"], ("position", "velocity", "rho")):
-        assert common.first_mismatch(a, b) is None, name
+    for path in ("tiles", "list"):
+        for a, b, name in zip(out[path], out["generic"], ("position", "velocity", "rho")):
+            assert common.first_mismatch(a, b) is None, (path, name)
     moved = np.abs(out["tiles"][0][liquid, :3] - pos[liquid, :3]).max()
     assert moved > 2.0, "the block did not move (max displacement %g)" % moved
 

@@ -12,12 +12,12 @@ pytestmark = pytest.mark.gpu
 slab = importlib.import_module(common.PKG + ".slab")
 
 
-@pytest.fixture(scope="module", autouse=True)
-def tiled_neighbors():
-    """Slab ranks of a bench-sized fluid take the tile kernel; the test scenes are small, so force it."""
+@pytest.fixture(scope="module", autouse=True, params=["list", "tiles"])
+def neighbor_path(request):
+    """Slab ranks run the ordinary kernels: the list kernel (the library's choice) and the tile kernel."""
     import os
     old = os.environ.get("SPH_NEIGHBOR_PATH")
-    os.environ["SPH_NEIGHBOR_PATH"] = "tiles"
+    os.environ["SPH_NEIGHBOR_PATH"] = request.param
     yield
     if old is None:
         os.environ.pop("SPH_NEIGHBOR_PATH", None)
