@@ -173,7 +173,15 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 // Nothing inexact reaches the output. A thread whose list overflows (LP_CAP hits, 8191 particles per cell) takes
 // find_neighbors_one. No barriers, full occupancy: the kernel runs at ~90 % issue utilisation.
 #define LP_THREADS 128
-#define LP_CAP 64
+// hit-list capacity and resident CTAs per SM the register allocation is tuned for: the kernel is bound by load
+// latency and the L1 data pipe, 12 CTAs (48 warps, 40 registers, 16 KB of shared memory each) measured fastest
+#ifndef LP_CAP
+#define LP_CAP 56
+#endif
+#ifndef LP_MINB
+#define LP_MINB 12
+#endif
+static_assert(LP_CAP <= 64, "the 6-bit histogram bins of the select phase hold at most 63 other particles");
 
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
 // 256-bit loads of a sweep pass share one address computation.
@@ -219,7 +227,7 @@ __device__ __forceinline__ void ld256u(const void *p, uint4 &a, uint4 &b) {
 }
 
 template <bool WITH_DENSITY, int VAR>
-__global__ void __launch_bounds__(LP_THREADS) k_find_neighbors_list(DevParams d, const float4 *__restrict__ sp,
+__global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(DevParams d, const float4 *__restrict__ sp,
                                                                     const float *__restrict__ S,
                                                                     const unsigned *__restrict__ cellStart,
                                                                     int *__restrict__ nb, float *__restrict__ rho,
