@@ -51,7 +51,7 @@ KERNEL_BYTES = {
 
 
 # profile name -> kernel whose ncu capture (profiles/*_ncu_full_summary.json) gives the measured DRAM traffic per launch
-NCU_KERNEL = {"find_neighbors+density": "k_find_neighbors_list<1,1>", "pressure_force+predict": "k_pressure_force<1>",
+NCU_KERNEL = {"find_neighbors+density": "k_find_neighbors_list<1,2>", "pressure_force+predict": "k_pressure_force<1>",
               "pressure_force+integrate": "k_pressure_force<2>", "predict_density+correct_pressure": "k_predict_density<1>"}
 
 

@@ -76,8 +76,9 @@ __device__ __forceinline__ size_t nb_index(int id, int k) {
 
 // Ids of slots [k0, k0 + 8) of particle id: eight independent, coalesced loads issued together. The hot loops
 // fetch the next eight while they work on the current eight, so no iteration waits for its id to arrive.
-__device__ __forceinline__ void nb_load8(const int *__restrict__ nb, int id, int k0, int (&v)[8]) {
+template <int B>
+__device__ __forceinline__ void nb_load8(const int *__restrict__ nb, int id, int k0, int (&v)[B]) {
   const int *p = nb + nb_index(id, k0);
 #pragma unroll
-  for (int j = 0; j < 8; j++) v[j] = __ldg(p + 32 * j);
+  for (int j = 0; j < B; j++) v[j] = __ldg(p + 32 * j);
 }

@@ -161,27 +161,36 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
   find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
 }
 
-// ---------------------------------------------------------------- list path
+// ---------------------------------------------------------------- list path (the product path)
 // One thread per particle, like the generic path, but the 8-cell scan is done ONCE:
-//   sweep   eight candidates per iteration from SoA copies of the sorted positions (three 256-bit loads), squared
-//           distances in Blackwell's packed fp32x2 pipe, a conservative filter (radius 31h/30 = the largest r_thr the
-//           reference can choose, slightly inflated, FMA allowed) and a branch-free append of (cell k, rank in cell)
-//           to the thread's hit list in shared memory — in scan order, because the thread walks its cells in the
-//           reference's visiting order;
-//   select  the ~35 hits are re-evaluated with the reference's operation order (exact distances from the float4
+//   group   the CTA's 128 consecutive particles are dealt to the threads grouped by (cell, octant), so that the
+//           lanes of a warp walk the same cells and load the same addresses (broadcast);
+//   sweep   16 candidates per iteration from a half-precision, cell-local copy of the sorted positions (three
+//           256-bit loads, k_soa_positions_half), packed HADD2/HFMA2 distances against a conservative filter radius
+//           (the largest r_thr the reference can choose, 31h/30, plus the fp16 error bound), the sign bits gathered
+//           into a 16-bit mask, and the (rare) hits appended as (cell k, rank in cell) to the thread's hit list in
+//           shared memory — in scan order, because the thread walks its cells in the reference's visiting order.
+//           Grids where a cell id could stand for two nearby cells (tiny or aliased grids, see launch_find_neighbors)
+//           sweep the fp32 copy instead (VAR 1; VAR 0 is the first, branchy version, kept for A/B runs);
+//   select  the ~38 hits are re-evaluated with the reference's operation order (exact distances from the float4
 //           sorted positions): histogram, r_thr, first 32 within r_thr, rho(t).
-// Nothing inexact reaches the output. A thread whose list overflows (LP_CAP hits, 8191 particles per cell) takes
-// find_neighbors_one. No barriers, full occupancy: the kernel runs at ~90 % issue utilisation.
+// Nothing inexact reaches the output. Hits beyond the shared-memory list spill to a per-thread array in local
+// memory; a thread whose neighbourhood exceeds that as well (or a cell with more than 8191 particles) takes
+// find_neighbors_one. The kernel is bound by the L1 data pipe (81 %) and instruction issue (83 %), see profiles/.
 #define LP_THREADS 128
 // hit-list capacity and resident CTAs per SM the register allocation is tuned for: the kernel is bound by load
-// latency and the L1 data pipe, 12 CTAs (48 warps, 40 registers, 16 KB of shared memory each) measured fastest
+// latency and the L1 data pipe; 10 CTAs (40 warps, 47 registers, 16 KB of shared memory each) measured fastest
 #ifndef LP_CAP
 #define LP_CAP 56
 #endif
 #ifndef LP_MINB
-#define LP_MINB 12
+#define LP_MINB 10
 #endif
-static_assert(LP_CAP <= 64, "the 6-bit histogram bins of the select phase hold at most 63 other particles");
+// hits beyond the shared-memory list go to a per-thread overflow array in local memory (denser-than-lattice
+// neighbourhoods, e.g. the settled config A); only beyond LP_CAP + LP_OVF does a thread rescan with the plain kernel
+#ifndef LP_OVF
+#define LP_OVF 72
+#endif
 
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
 // 256-bit loads of a sweep pass share one address computation.
@@ -291,6 +300,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr (j == 30)
   const float rfilt2 = rmaxf * rmaxf * 1.0001f;
   const float2 npx = make_float2(-pos.x, -pos.x), npy = make_float2(-pos.y, -pos.y), npz = make_float2(-pos.z, -pos.z);
+  unsigned short ovf[LP_OVF];
   int n = 0;
   if (fits && VAR == 2) {
     // half-precision variant: 16 candidates per pass from the cell-local fp16 copy (three 256-bit loads = half the
@@ -336,7 +346,9 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
         while (m) {
           const int i = __ffs(m);  // 1-based bit; bits 17..24 are candidates 9..16 (1-based)
           m &= m - 1u;
-          hits[min(nh, LP_CAP)][tid] = (unsigned short)(v0 + i - ((i > 16) ? 8 : 0));  // row LP_CAP = overflow, never read
+          const unsigned short hv = (unsigned short)(v0 + i - ((i > 16) ? 8 : 0));
+          hits[min(nh, LP_CAP)][tid] = hv;  // row LP_CAP is never read
+          if (nh >= LP_CAP) ovf[min(nh - LP_CAP, LP_OVF - 1)] = hv;
           nh++;
         }
       }
@@ -377,7 +389,9 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
         while (m) {
           const int i = __ffs(m);
           m &= m - 1u;
-          hits[min(nh, LP_CAP)][tid] = (unsigned short)(v0 + i);  // row LP_CAP = overflow, never read
+          const unsigned short hv = (unsigned short)(v0 + i);
+          hits[min(nh, LP_CAP)][tid] = hv;  // row LP_CAP is never read
+          if (nh >= LP_CAP) ovf[min(nh - LP_CAP, LP_OVF - 1)] = hv;
           nh++;
         }
       }
@@ -405,25 +419,31 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
         const float2 d2 = pair(xb.x, xb.y, yb.x, yb.y, zb.x, zb.y), d3 = pair(xb.z, xb.w, yb.z, yb.w, zb.z, zb.w);
         // the group is aligned to 8: its ends may reach into the neighbouring cells, masked by the rank test
         auto keep = [&](float dd, int i) {
-          if (dd <= rfilt2 && (unsigned)(j + i - b) < len) { if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + i); n++; }
+          if (dd <= rfilt2 && (unsigned)(j + i - b) < len) {
+            if (n < LP_CAP) hits[n][tid] = (unsigned short)(enc + j + i);
+            else ovf[min(n - LP_CAP, LP_OVF - 1)] = (unsigned short)(enc + j + i);
+            n++;
+          }
         };
         keep(d0.x, 0); keep(d0.y, 1); keep(d1.x, 2); keep(d1.y, 3);
         keep(d2.x, 4); keep(d2.y, 5); keep(d3.x, 6); keep(d3.y, 7);
       }
     }
   }
-  if (!fits || n > LP_CAP) {
+  if (!fits || n > LP_CAP + LP_OVF) {
     find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
     return;
   }
   // exact distances of the hits (the particle itself is among them: skipped by index)
-  auto hit_index = [&](int t) { const unsigned hv = hits[t][tid]; return cb[hv >> 13] + (int)(hv & 8191u); };
+  auto hit_index = [&](unsigned hv) { return cb[hv >> 13] + (int)(hv & 8191u); };
   auto dist2 = [&](int j) {
     const float4 q = ldg4(sp + j);
     const float ex = pos.x - q.x, ey = pos.y - q.y, ez = pos.z - q.z;
     return ex * ex + ey * ey + ez * ez;
   };
-  unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull;  // 30 bins x 6 bits; n <= 64 hits, one is the particle itself
+  // 30 bins x 7 bits, 8 bins per word: at most LP_CAP + LP_OVF - 1 = 127 other particles, no bin can overflow
+  static_assert(LP_CAP + LP_OVF <= 128, "7-bit histogram bins");
+  unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull, hist3 = 0ull;
   const float h2 = d.h * d.h;
   int found = 0;
   double density = 0.0;
@@ -441,9 +461,9 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   // smaller r_thr: the exact distances are gathered once for most lanes.
   const float r2open = ((float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS) *
                        ((float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS);
-  for (int t = 0; t < n; t++) {
-    const int j = hit_index(t);
-    if (j == id) continue;
+  auto first_pass = [&](unsigned hv) {
+    const int j = hit_index(hv);
+    if (j == id) return;
     const float dd = dist2(j);
     if (dd <= h2) {
       float sq;
@@ -451,23 +471,27 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
       int e = min((int)(sq * d.binScale), SPH_RADIUS_SEGMENTS);
       const int bin = e + ((dd >= d.binT[e + 1]) ? 1 : 0) - ((dd < d.binT[e]) ? 1 : 0);
       if (bin < SPH_RADIUS_SEGMENTS) {
-        const int w = (bin >= 10 ? 1 : 0) + (bin >= 20 ? 1 : 0);
-        const unsigned long long inc = 1ull << ((bin - 10 * w) * 6);
+        const int w = bin >> 3;
+        const unsigned long long inc = 1ull << ((bin & 7) * 7);
         hist0 += (w == 0) ? inc : 0ull;
         hist1 += (w == 1) ? inc : 0ull;
         hist2 += (w == 2) ? inc : 0ull;
+        hist3 += (w == 3) ? inc : 0ull;
       }
     }
     if (dd <= r2open && found < SPH_NB) take(j, dd);
-  }
+  };
+  const int nList = min(n, LP_CAP);
+  for (int t = 0; t < nList; t++) first_pass(hits[t][tid]);
+  for (int t = LP_CAP; t < n; t++) first_pass(ovf[t - LP_CAP]);
   int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
   {
     int sum = 0;
     bool open = true;
 #pragma unroll
     for (int jj = 0; jj < SPH_RADIUS_SEGMENTS; jj++) {
-      const unsigned long long hw = jj < 10 ? hist0 : (jj < 20 ? hist1 : hist2);
-      sum += (int)((hw >> ((jj % 10) * 6)) & 63ull);
+      const unsigned long long hw = jj < 8 ? hist0 : (jj < 16 ? hist1 : (jj < 24 ? hist2 : hist3));
+      sum += (int)((hw >> ((jj & 7) * 7)) & 127ull);
       if (open && sum >= SPH_NB) { jthr = (sum == SPH_NB) ? jj : jj - 1; open = false; }
     }
   }
@@ -477,7 +501,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     found = 0;
     density = 0.0;
     for (int t = 0; t < n && found < SPH_NB; t++) {
-      const int j = hit_index(t);
+      const int j = hit_index((t < LP_CAP) ? hits[t][tid] : ovf[t - LP_CAP]);
       if (j == id) continue;
       const float dd = dist2(j);
       if (dd <= r2) take(j, dd);
