@@ -25,6 +25,7 @@ struct SlabState {
   unsigned *gid, *gidAlt;
   float4 *posAlt, *velAlt;
   int *counters, *hostCounters;   // 8 ints: migD, ghostD, migU, ghostU, keep, flags
+  int *hostCountersDev;           // device-side address of the pinned hostCounters
   int *sendList[2];               // local original indices of the particles a neighbour holds as ghosts
   int migOut[2], ghostOut[2];
   const SlabRec *myMig[2];
@@ -87,6 +88,11 @@ __global__ void __launch_bounds__(256) k_slab_append(SlabAppend a, float4 *__res
   }
 }
 
+__global__ void k_slab_publish(const int *__restrict__ counters, volatile int *hostCounters) {
+  if (threadIdx.x < 8) hostCounters[threadIdx.x] = counters[threadIdx.x];
+  __threadfence_system();
+}
+
 __global__ void __launch_bounds__(256) k_slab_iota(int *__restrict__ dst, int n, int first) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[i] = first + i;
@@ -144,6 +150,7 @@ int sph_slab_begin(sph_ctx *c, int n_owned, const uint32_t *gid, int z0, int z1,
   SCU(cudaMalloc(&s->posAlt, 32 * cap)); SCU(cudaMalloc(&s->velAlt, 32 * cap));
   SCU(cudaMemset(s->posAlt, 0, 32 * cap)); SCU(cudaMemset(s->velAlt, 0, 32 * cap));
   SCU(cudaMalloc(&s->counters, 32)); SCU(cudaMallocHost(&s->hostCounters, 32));
+  SCU(cudaHostGetDevicePointer((void **)&s->hostCountersDev, s->hostCounters, 0));
   SCU(cudaMalloc(&s->sendList[0], 4 * (size_t)(halo_cap + mig_cap)));
   SCU(cudaMalloc(&s->sendList[1], 4 * (size_t)(halo_cap + mig_cap)));
   SCU(cudaMemcpy(s->gid, gid, 4 * (size_t)n_owned, cudaMemcpyHostToDevice));
@@ -167,7 +174,9 @@ int sph_slab_classify(sph_ctx *c, void *mig_down, void *ghost_down, void *mig_up
                                                         s->gidAlt, (SlabRec *)mig_down, (SlabRec *)ghost_down,
                                                         (SlabRec *)mig_up, (SlabRec *)ghost_up, s->sendList[0],
                                                         s->sendList[1], s->counters);
-  SCU(cudaMemcpyAsync(s->hostCounters, s->counters, 32, cudaMemcpyDeviceToHost, c->stream));
+  // the counts go to pinned host memory through a store, not a copy: a device-to-host memcpy would queue on the DMA
+  // engine behind a pipelined read-back of 130 MB (sph_slab_read_owned_begin) and stall every step by its duration
+  k_slab_publish<<<1, 32, 0, c->stream>>>(s->counters, s->hostCountersDev);
   SCU(cudaStreamSynchronize(c->stream));
   const int *h = s->hostCounters;
   if (h[5]) return slab_fail(h[5] & 1 ? "a particle crossed more than one cell layer in one step"
