@@ -66,6 +66,7 @@ struct sph_ctx {
   void *profiler;              // Profiler* when per-kernel event timing is on
   SlabState *slab;             // non-null: this context is one slab rank of a multi-device fluid (sph_slab.cu)
   unsigned *rankKey;           // in-cell ranking key per original index (global ids of a slab rank); null = the index itself
+  unsigned *tmpRankKey;        // slab ranks: rankKey in scatter order (written next to tmpSerial), N words
   cudaStream_t ownStream;      // the stream created with the context (c->stream may be replaced by sph_set_stream)
   long long launches;          // kernels launched by sph_step so far
   // pipelined read-back (sph_read_begin / sph_read_end): a device-to-host copy of position or velocity that

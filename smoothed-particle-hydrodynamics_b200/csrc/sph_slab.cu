@@ -149,6 +149,7 @@ int sph_slab_begin(sph_ctx *c, int n_owned, const uint32_t *gid, int z0, int z1,
   SCU(cudaMalloc(&s->gid, 4 * cap)); SCU(cudaMalloc(&s->gidAlt, 4 * cap));
   SCU(cudaMalloc(&s->posAlt, 32 * cap)); SCU(cudaMalloc(&s->velAlt, 32 * cap));
   SCU(cudaMemset(s->posAlt, 0, 32 * cap)); SCU(cudaMemset(s->velAlt, 0, 32 * cap));
+  SCU(cudaMalloc(&c->tmpRankKey, 4 * cap));
   SCU(cudaMalloc(&s->counters, 32)); SCU(cudaMallocHost(&s->hostCounters, 32));
   SCU(cudaHostGetDevicePointer((void **)&s->hostCountersDev, s->hostCounters, 0));
   SCU(cudaMalloc(&s->sendList[0], 4 * (size_t)(halo_cap + mig_cap)));

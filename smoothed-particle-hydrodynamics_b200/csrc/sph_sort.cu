@@ -122,13 +122,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_cells(unsigned *__restric
 // ---------------------------------------------------------------- scatter into cells (order inside a cell arbitrary)
 __global__ void __launch_bounds__(256) k_scatter(DevParams d, const unsigned *__restrict__ key,
                                                  const unsigned *__restrict__ cellStart, unsigned *__restrict__ cursor,
-                                                 unsigned *__restrict__ tmpSerial) {
+                                                 unsigned *__restrict__ tmpSerial,
+                                                 const unsigned *__restrict__ rankKey, unsigned *__restrict__ tmpRankKey) {
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= d.N) return;
   unsigned cell = key[id];
   unsigned bin = cell < (unsigned)d.G ? cell : (unsigned)d.G - 1u;
   unsigned slot = cellStart[bin] + atomicAdd(&cursor[bin], 1u);
   tmpSerial[slot] = (unsigned)id;
+  if (rankKey) tmpRankKey[slot] = rankKey[id];  // slab ranks: the ranking key travels with the serial id
 }
 
 // ---------------------------------------------------------------- rank inside the cell (+ sortPostPass gather)
@@ -156,9 +158,9 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
   unsigned rank = 0;
   // order within a cell = ascending original index (glibc's stable merge sort in _runSort); a slab rank
   // ranks by GLOBAL id instead, which is the original index of the single-device run
-  if (rankKey) {
-    const unsigned mine = rankKey[serial];
-    for (unsigned t = b; t < e; ++t) rank += (rankKey[tmpSerial[t]] < mine) ? 1u : 0u;
+  if (rankKey) {  // rankKey = the keys in scatter order (tmpRankKey), contiguous per cell
+    const unsigned mine = rankKey[s];
+    for (unsigned t = b; t < e; ++t) rank += (rankKey[t] < mine) ? 1u : 0u;
   } else {
     for (unsigned t = b; t < e; ++t) rank += (tmpSerial[t] < serial) ? 1u : 0u;
   }
@@ -229,17 +231,19 @@ void launch_sort(sph_ctx *c, bool fuse_reorder) {
   unsigned ticketBase = (c->epoch - 1u) * (unsigned)c->scanTiles;
   k_scan_cells<<<c->scanTiles, SCAN_THREADS, 0, c->stream>>>(c->cellCount, c->cellStart, n, c->scanState, c->scanTicket,
                                                              ticketBase, c->epoch, c->cellListCount);
-  k_scatter<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->cellCount, c->tmpSerial);
+  k_scatter<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->cellCount, c->tmpSerial, c->rankKey,
+                                                       c->tmpRankKey);
+  const unsigned *rk = c->rankKey ? c->tmpRankKey : nullptr;
   if (fuse_reorder)
     k_rank_reorder<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                    c->particleIndex, c->particleIndexBack, c->position,
                                                                    c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey, c->recA, c->recB);
+                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount, rk, c->recA, c->recB);
   else
     k_rank_reorder<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
                                                                     c->particleIndex, c->particleIndexBack, c->position,
                                                                     c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount, c->rankKey, c->recA, c->recB);
+                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount, rk, c->recA, c->recB);
 }
 
 void launch_reorder(sph_ctx *c) {
