@@ -516,7 +516,8 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   }
 }
 
-// ---------------------------------------------------------------- tiled path (the product path)
+// ---------------------------------------------------------------- tiled path (round-1 design, superseded by the list
+// path above; kept as an independent implementation for the parity tests and A/B runs: SPH_NEIGHBOR_PATH=tiles|auto)
 // One persistent kernel, k_neighbor_tiles. A CTA takes a HOME BLOCK = the two hash cells (2b, 2b+1),
 // whose particles are one contiguous range of the sorted arrays, and
 //   stage   copies the positions of the 4x3x3 = 36 surrounding cells (offsets -1..2 in id, -1..1 in
