@@ -1036,6 +1036,8 @@ static void launch_tiles(sph_ctx *c) {
 }
 
 void launch_find_neighbors(sph_ctx *c, bool with_density) {
+  // Default: the list kernel (below). SPH_NEIGHBOR_PATH=tiles|generic force the earlier implementations, =auto the
+  // round-1 policy (tiles for fluids of >= 131 072 particles, watched by their own statistics).
   // the tiled kernel assumes the 36 cells around a home block are distinct: true for grids >= 4 x 3 x 3.
   // Below ~1000 home blocks (two per resident CTA) its persistent CTAs do not balance and the plain scan wins
   // (config A, 61 k particles: 0.17 ms against 0.32 ms).
