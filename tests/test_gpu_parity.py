@@ -173,6 +173,33 @@ def test_ragged_and_tiny(P, O):
     _fused_vs_oracle(P, O, cfg2, 2)
 
 
+@pytest.mark.parametrize("per_h3", [8, 24, 48])
+def test_random_gas_neighbor_search_and_step(P, O, per_h3):
+    """Uniformly random positions (no lattice): distances fall anywhere relative to r_thr and to the cell faces,
+    which is what the list kernel's half-precision pre-filter has to be conservative about. 8 particles per h^3 is
+    the rest density (~38 hits per particle), 24 fills the shared-memory hit list and spills into the per-thread
+    overflow array, 48 exceeds that too (the thread rescans with the plain kernel)."""
+    h, r0 = 3.34, 1.67
+    box = (32, 28, 40)                                  # in r0: 16 h x 14 h x 20 h
+    shell, shell_v = common.synthetic_block(1, 1, 1, box, seed=1)
+    shell, shell_v = shell[1:], shell_v[1:]             # the boundary particles only
+    rng = np.random.RandomState(100 + per_h3)
+    n = int(per_h3 * (box[0] - 2) * (box[1] - 2) * (box[2] - 2) / 8)
+    pos = np.zeros((n, 4), np.float32)
+    pos[:, :3] = (r0 + rng.uniform(0, 1, size=(n, 3)) * (np.asarray(box, np.float64) - 2) * r0).astype(np.float32)
+    pos[:, 3] = np.float32(1.1)
+    pos = np.concatenate([pos, shell]); vel = np.concatenate([np.zeros((n, 4), np.float32), shell_v])
+    cfg = dict(params=common.fill_counts(P.default_params(box=(box[0] // 2, box[1] // 2, box[2] // 2)), pos),
+               position=pos, velocity=vel)
+    a, b = common.create(P, cfg), common.create(O, cfg)
+    for st in common.stage_order(cfg["params"].max_iteration)[:8]:   # ... FIND_NEIGHBORS, COMPUTE_DENSITY
+        a.stage(st); b.stage(st)
+    _cmp(a, b, "neighborMap", "random gas %d/h^3" % per_h3)
+    _cmp(a, b, "rho", "random gas %d/h^3" % per_h3, "first")
+    a.close(); b.close()
+    _fused_vs_oracle(P, O, cfg, 2)
+
+
 def test_read_write_roundtrip_and_errors(P):
     cfg = common.config_a(P)
     ctx = common.create(P, cfg)
