@@ -223,6 +223,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
     c->force_tiled_neighbors = q && !strcmp(q, "tiles");
     c->force_list_neighbors = q && !strcmp(q, "list");
     c->auto_tiles = q && !strcmp(q, "auto");
+    const char *dg = getenv("SPH_DEEP_GATHER");
+    c->deep_gather = dg ? atoi(dg) : -1;
     const char *lv = getenv("SPH_LIST_VARIANT");
     c->list_variant = lv ? atoi(lv) : 2;
   }

@@ -50,6 +50,7 @@ struct sph_ctx {
   int nbMode;                   // 0 = not decided yet, 1 = tiles, 2 = plain scan (with a probing tile launch every 64 steps)
   bool force_list_neighbors;    // SPH_NEIGHBOR_PATH=list: single-sweep hit-list kernel
   bool auto_tiles;               // SPH_NEIGHBOR_PATH=auto: the round-1 policy (tiles for large fluids, watched by the statistics)
+  int deep_gather;              // SPH_DEEP_GATHER=0|1 forces / forbids the latency-optimised gather kernels; -1 = by size
   int list_variant;             // SPH_LIST_VARIANT: sweep variant of the list kernel (experiments)
   float *soa;                   // 3 (Npad + 32): sweep copy of the sorted positions, groups of 8 as x[8] | y[8] | z[8] (k_soa_positions)
   bool force_tiled_neighbors;   // SPH_NEIGHBOR_PATH=tiles: the tile kernel whatever the particle count (grid permitting)

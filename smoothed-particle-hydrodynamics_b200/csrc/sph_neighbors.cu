@@ -177,7 +177,9 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 // Nothing inexact reaches the output. Hits beyond the shared-memory list spill to a per-thread array in local
 // memory; a thread whose neighbourhood exceeds that as well (or a cell with more than 8191 particles) takes
 // find_neighbors_one. The kernel is bound by the L1 data pipe (81 %) and instruction issue (83 %), see profiles/.
+#ifndef LP_THREADS
 #define LP_THREADS 128
+#endif
 // hit-list capacity and resident CTAs per SM the register allocation is tuned for: the kernel is bound by load
 // latency and the L1 data pipe; 10 CTAs (40 warps, 47 registers, 16 KB of shared memory each) measured fastest
 #ifndef LP_CAP
