@@ -393,7 +393,7 @@ int sph_step(sph_ctx *c) {
     { ProfScope s(c, last ? PK_PRESSURE_FORCE_INTEGRATE : PK_PRESSURE_FORCE); launch_pressure_force(c, last ? 2 : 1); }
   }
   const int mem = fused_membranes(c);
-  c->launches += 8 + mem + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
+  c->launches += 7 + mem + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
   return check_launch(c, false);
 }
 
