@@ -152,6 +152,12 @@ static cudaError_t dalloc(T **ptr, size_t count, bool zero = true) {
 
 extern "C" int sph_profile_enable(sph_ctx *c, int on);
 
+static void drop_graph(sph_ctx *c) {
+  for (int h = 0; h < 2; h++)
+    if (c->stepGraph[h]) { cudaGraphExecDestroy(c->stepGraph[h]); c->stepGraph[h] = nullptr; }
+}
+
+
 extern "C" {
 
 void sph_destroy(sph_ctx *c) {
@@ -166,6 +172,7 @@ void sph_destroy(sph_ctx *c) {
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
+  drop_graph(c);
   if (c->copyStream) {
     cudaStreamSynchronize(c->copyStream);
     cudaStreamDestroy(c->copyStream);
@@ -189,6 +196,12 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   if (!p || !pos4 || !vel4 || p->particle_count <= 0 || p->grid_cell_count <= 0 || p->grid_cells_x <= 0 ||
       p->grid_cells_y <= 0 || p->muscle_count < 0) {
     fail(SPH_E_INVALID, "sph_create: bad arguments");
+    return nullptr;
+  }
+  if (p->grid_cell_count > (1 << 24)) {
+    // the sorted cell id travels as a float in sortedPosition.w (the reference's layout, sphFluid.cl:457-465):
+    // exact up to 2^24 only. The reference itself masks ids to 16 bits.
+    fail(SPH_E_INVALID, "sph_create: grid_cell_count > 2^24 (cell ids are carried as floats in sortedPosition.w)");
     return nullptr;
   }
   int ndev = 0;
@@ -222,11 +235,16 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
     c->force_generic_neighbors = (e && e[0] == '1') || (q && !strcmp(q, "generic"));
     c->force_tiled_neighbors = q && !strcmp(q, "tiles");
     c->force_list_neighbors = q && !strcmp(q, "list");
+    c->force_coop_neighbors = q && !strcmp(q, "coop");
     c->auto_tiles = q && !strcmp(q, "auto");
     const char *dg = getenv("SPH_DEEP_GATHER");
     c->deep_gather = dg ? atoi(dg) : -1;
     const char *lv = getenv("SPH_LIST_VARIANT");
     c->list_variant = lv ? atoi(lv) : 2;
+    const char *gm = getenv("SPH_GRAPH");
+    c->graph_mode = gm ? atoi(gm) : -1;
+    const char *ln = getenv("SPH_LANES");
+    c->lanes = ln ? atoi(ln) : 0;
   }
   bool ok = true;
 #define A(x) ok = ok && ((e = (x)) == cudaSuccess)
@@ -369,31 +387,84 @@ static int fused_membranes(sph_ctx *c) {
   if (c->has_pml) {
     ProfScope s(c, PK_MEMBRANES);
     launch_membrane_interaction(c, true);
-    return 1;
+    return 2;
   }
-  if (c->dispDirty) {
+  if (c->dispDirty) {  // clearMembraneBuffers zeroes both upper halves (sphFluid.cl:1224-1225)
     cudaMemsetAsync(c->position + c->d.N, 0, 16 * (size_t)c->d.N, c->stream);
+    cudaMemsetAsync(c->velocity + c->d.N, 0, 16 * (size_t)c->d.N, c->stream);
     c->dispDirty = false;
   }
+  return 0;
+}
+
+// The kernels of one fused step, in order, on c->stream, in two halves: everything up to the last density
+// prediction, and the kernels that rewrite position / velocity (pressure force + integrate, membranes). A
+// pipelined read-back of the previous step's positions only has to be over before the second half starts.
+static int step_body(sph_ctx *c, int half) {
+  const int iters = c->p.max_iteration < 1 ? 1 : c->p.max_iteration;  // do{}while: at least one pass
+  const bool elastic = c->d.numElastic > 0 && c->has_elastic;
+  if (half == 0) {
+    { ProfScope s(c, PK_HASH); launch_hash_count(c, false); }
+    { ProfScope s(c, PK_SORT); launch_sort(c, true); }
+    { ProfScope s(c, PK_NEIGHBORS); launch_find_neighbors(c, true); }
+    { ProfScope s(c, PK_FORCES); launch_forces(c, true); }
+    if (elastic) { ProfScope s(c, PK_ELASTIC); launch_elastic(c); }
+    for (int it = 0; it < iters; it++) {
+      { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); }
+      if (it + 1 < iters) { ProfScope s(c, PK_PRESSURE_FORCE); launch_pressure_force(c, 1); }
+    }
+    return 7 + (elastic ? 1 : 0) + 2 * iters - 1;
+  }
+  { ProfScope s(c, PK_PRESSURE_FORCE_INTEGRATE); launch_pressure_force(c, 2); }
+  return 1 + fused_membranes(c);
+}
+
+#ifndef SPH_GRAPH_MAX_N
+#define SPH_GRAPH_MAX_N (1 << 21)   // above this a step is milliseconds long and launch gaps do not show
+#endif
+
+static bool want_graph(const sph_ctx *c) {
+  if (c->profiler || c->slab || c->auto_tiles || c->force_tiled_neighbors) return false;  // per-kernel events / host-side decisions in the step
+  return c->graph_mode < 0 ? c->d.N <= SPH_GRAPH_MAX_N : c->graph_mode != 0;
+}
+
+static int capture_half(sph_ctx *c, int half) {
+  cudaGraph_t g = nullptr;
+  CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+  c->capturing = true;
+  c->graphNodes[half] = step_body(c, half);
+  c->capturing = false;
+  cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+  if (e != cudaSuccess || !g) return fail(SPH_E_DEVICE, std::string("sph_step: stream capture failed: ") + cudaGetErrorString(e));
+  e = cudaGraphInstantiate(&c->stepGraph[half], g, 0);
+  cudaGraphDestroy(g);
+  if (e != cudaSuccess) { c->stepGraph[half] = nullptr; return fail(SPH_E_DEVICE, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
   return 0;
 }
 
 int sph_step(sph_ctx *c) {
   if (!c) return fail(SPH_E_INVALID, "null ctx");
   CU(cudaSetDevice(c->device));
-  { ProfScope s(c, PK_HASH); launch_hash_count(c, false); }
-  { ProfScope s(c, PK_SORT); launch_sort(c, true); }
-  { ProfScope s(c, PK_NEIGHBORS); launch_find_neighbors(c, true); }
-  { ProfScope s(c, PK_FORCES); launch_forces(c, true); }
-  if (c->d.numElastic > 0 && c->has_elastic) { ProfScope s(c, PK_ELASTIC); launch_elastic(c); }
-  const int iters = c->p.max_iteration < 1 ? 1 : c->p.max_iteration;  // do{}while: at least one pass
-  for (int it = 0; it < iters; it++) {
-    { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); }
-    const bool last = it + 1 == iters;
-    { ProfScope s(c, last ? PK_PRESSURE_FORCE_INTEGRATE : PK_PRESSURE_FORCE); launch_pressure_force(c, last ? 2 : 1); }
+  if (!want_graph(c)) {
+    c->launches += step_body(c, 0);
+    c->launches += step_body(c, 1);
+    return check_launch(c, false);
   }
-  const int mem = fused_membranes(c);
-  c->launches += 7 + mem + 2 * iters + ((c->d.numElastic > 0 && c->has_elastic) ? 1 : 0);
+  // Graph replay: small scenes are launch-bound (a dozen dependent kernels of a few microseconds each). What a
+  // replay cannot carry sits between the two graphs: the wait for a pipelined read-back, and the once-per-upload
+  // clearing of the displacement halves in front.
+  if (!c->has_pml && c->dispDirty) fused_membranes(c);
+  if (c->stepGraph[0] && c->graphStream != c->stream) drop_graph(c);
+  if (!c->stepGraph[0]) {
+    int rc = capture_half(c, 0);
+    if (!rc) rc = capture_half(c, 1);
+    if (rc) { drop_graph(c); return rc; }
+    c->graphStream = c->stream;
+  }
+  CU(cudaGraphLaunch(c->stepGraph[0], c->stream));
+  read_fence(c);
+  CU(cudaGraphLaunch(c->stepGraph[1], c->stream));
+  c->launches += c->graphNodes[0] + c->graphNodes[1];
   return check_launch(c, false);
 }
 
@@ -649,7 +720,7 @@ int sph_write(sph_ctx *c, int id, const void *src, size_t bytes) {
   if (bytes > have) return fail(SPH_E_SIZE, "sph_write: too many bytes");
   CU(cudaSetDevice(c->device));
   read_fence(c);
-  if (id == SPH_BUF_POSITION) c->dispDirty = true;
+  c->dispDirty = true;  // position or velocity: the upper half may have been overwritten
   CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
   CU(cudaStreamSynchronize(c->stream));
   return 0;

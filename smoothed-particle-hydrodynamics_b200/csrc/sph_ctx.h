@@ -49,6 +49,7 @@ struct sph_ctx {
   int genericHold;
   int nbMode;                   // 0 = not decided yet, 1 = tiles, 2 = plain scan (with a probing tile launch every 64 steps)
   bool force_list_neighbors;    // SPH_NEIGHBOR_PATH=list: single-sweep hit-list kernel
+  bool force_coop_neighbors;    // SPH_NEIGHBOR_PATH=coop: eight lanes per particle (default for small scenes)
   bool auto_tiles;               // SPH_NEIGHBOR_PATH=auto: the round-1 policy (tiles for large fluids, watched by the statistics)
   int deep_gather;              // SPH_DEEP_GATHER=0|1 forces / forbids the latency-optimised gather kernels; -1 = by size
   int list_variant;             // SPH_LIST_VARIANT: sweep variant of the list kernel (experiments)
@@ -70,6 +71,14 @@ struct sph_ctx {
   unsigned *tmpRankKey;        // slab ranks: rankKey in scatter order (written next to tmpSerial), N words
   cudaStream_t ownStream;      // the stream created with the context (c->stream may be replaced by sph_set_stream)
   long long launches;          // kernels launched by sph_step so far
+  // CUDA graph of the fused step (small scenes are launch-bound: 13 dependent kernels of a few microseconds).
+  // Captured once per (context, stream); SPH_GRAPH=0|1 forbids / forces it, default: scenes below SPH_GRAPH_MAX_N.
+  cudaGraphExec_t stepGraph[2]; // the two halves of the step (see step_body)
+  cudaStream_t graphStream;    // the stream stepGraph was captured on
+  int graphNodes[2];           // kernels in each captured half
+  int graph_mode;              // -1 = by size, 0 = never, 1 = always
+  bool capturing;              // inside stream capture: launchers must not touch events of other streams
+  int lanes;                   // SPH_LANES: lanes per particle of the small-scene gather kernels (0 = by size)
   // pipelined read-back (sph_read_begin / sph_read_end): a device-to-host copy of position or velocity that
   // runs on its own stream while the next step computes; the integration kernel waits for it (read_fence)
   cudaStream_t copyStream;
@@ -85,7 +94,7 @@ struct sph_ctx {
 
 // order the next writer of position / velocity after a pending pipelined read of them
 static inline void read_fence(sph_ctx *c) {
-  if (c->readPending) cudaStreamWaitEvent(c->stream, c->evReadDone, 0);
+  if (c->readPending && !c->capturing) cudaStreamWaitEvent(c->stream, c->evReadDone, 0);
 }
 
 // sph_sort.cu
@@ -106,6 +115,10 @@ void launch_predict_density(sph_ctx *c, bool fuse_correct);
 void launch_correct_pressure(sph_ctx *c);
 void launch_pressure_force(sph_ctx *c, int mode);  // 0 = force only, 1 = + predictPositions, 2 = + integrate
 void launch_integrate(sph_ctx *c);
+// sph_lanes.cu: several lanes per particle (small scenes); false = no instantiation for this L
+bool launch_forces_lanes(sph_ctx *c, int L);
+bool launch_predict_density_lanes(sph_ctx *c, int L);
+bool launch_pressure_force_lanes(sph_ctx *c, int mode, int L);
 // sph_slab.cu
 void slab_destroy(sph_ctx *c);
 // sph_membranes.cu

@@ -1,0 +1,259 @@
+// sph_lanes.cu — the gather kernels of the fused step with SEVERAL LANES PER PARTICLE, for scenes that do not
+// fill the GPU with one thread per particle (the reference's own scenes: 61 k and 233 k particles).
+//
+// With one thread per particle such a launch is a single partial wave of CTAs and lasts as long as one thread's
+// chain of 32 dependent gathers. Here L lanes share a particle: lane l evaluates the neighbour slots l, l + L, ...
+// (32 / L independent gathers, all requested at once), the per-slot terms go to shared memory, and the sums are
+// then formed SEQUENTIALLY IN SLOT ORDER 0..31 by one lane per component — the reference's do{}while(++nc<32)
+// order, so the results stay bit-identical (terms the reference skips are added as +0, see sph_terms.cuh).
+// Same per-neighbour device functions as sph_pcisph.cu.
+#include "sph_ctx.h"
+#include "sph_terms.cuh"
+
+#define LN_THREADS 256
+
+// shared-memory layout of the term table: element (component c, particle pl, slot k) at c * CS + pl * S + k with
+// S = 32 + L and CS = P * S + 1: the L x (32 / L) lanes of a warp write distinct banks, and so do the summing lanes.
+template <int L> struct LaneGeom {
+  static constexpr int T = L <= 4 ? 128 : LN_THREADS;  // threads per CTA (the L = 4 term table of 256 threads exceeds 48 KB)
+  static constexpr int P = T / L;            // particles per CTA
+  static constexpr int S = 32 + L;
+  static constexpr int CS = P * S + 1;
+  static constexpr int SLOTS = SPH_NB / L;    // slots per lane
+};
+
+template <int L>
+__global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, const float4 *__restrict__ sp,
+                                                             const float4 *__restrict__ sv,
+                                                             const float *__restrict__ sortedType,
+                                                             const int *__restrict__ nb, const float *__restrict__ rho,
+                                                             float4 *__restrict__ acc, float *__restrict__ pressure,
+                                                             float4 *__restrict__ spPred, const float4 *__restrict__ recA,
+                                                             float4 *__restrict__ recB) {
+  using G = LaneGeom<L>;
+  __shared__ float term[6 * G::CS];
+  const int t = threadIdx.x, pl = t / L, l = t % L;
+  const int id = blockIdx.x * G::P + pl;
+  const bool live = id < d.N;
+  float4 pi = f4(0.f, 0.f, 0.f, 0.f), vi = pi;
+  bool active = false;
+  if (live) {
+    pi = sp[id];
+    active = !is_boundary(sortedType[id]);
+  }
+  if (active) {
+    vi = sv[id];
+    int jd[G::SLOTS];
+    float4 Pj[G::SLOTS], Vj[G::SLOTS];
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) jd[i] = __ldg(nb + nb_index(id, l + L * i));
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) ld256(recA + 2 * (size_t)(jd[i] != SPH_NO_ID ? jd[i] : id), Pj[i], Vj[i]);
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) {
+      float a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (jd[i] != SPH_NO_ID && !forces_term(d, pi, vi, Pj[i], Vj[i], a[0], a[1], a[2], a[3], a[4], a[5]))
+        a[0] = a[1] = a[2] = a[3] = a[4] = a[5] = 0.f;
+      float *o = term + pl * G::S + l + L * i;
+#pragma unroll
+      for (int c = 0; c < 6; c++) o[c * G::CS] = a[c];
+    }
+  }
+  __syncthreads();
+  // lane c < 3 sums component c of the viscosity sum and of the surface-tension sum, slots in order
+  float s = 0.f, u = 0.f;
+  if (active && l < 3) {
+    const float *a = term + l * G::CS + pl * G::S, *b = a + 3 * G::CS;
+#pragma unroll 8
+    for (int k = 0; k < SPH_NB; k++) { s += a[k]; u += b[k]; }
+  }
+  const int base = (t & 31) - l;
+  const float sx = __shfl_sync(0xffffffffu, s, base), sy = __shfl_sync(0xffffffffu, s, base + 1),
+              sz = __shfl_sync(0xffffffffu, s, base + 2);
+  const float tx = __shfl_sync(0xffffffffu, u, base), ty = __shfl_sync(0xffffffffu, u, base + 1),
+              tz = __shfl_sync(0xffffffffu, u, base + 2);
+  if (!live || l != 0) return;
+  const float4 zero = f4(0.f, 0.f, 0.f, 0.f);
+  if (!active) {  // boundary particle, as in k_forces
+    acc[id] = zero;
+    acc[d.N + id] = zero;
+    pressure[id] = 0.f;
+    recB[2 * (size_t)id + 1] = zero;
+    spPred[id] = pi;
+    return;
+  }
+  const float cv = d.massMu * (float)(d.del2W / (double)rho[id]);         // :688
+  float4 a = f4(sx * cv, sy * cv, sz * cv, 0.f);
+  a = a + f4(d.gravx, d.gravy, d.gravz, 0.f);
+  a = a + f4(tx, ty, tz, 0.f);
+  acc[id] = a;
+  acc[d.N + id] = zero;
+  pressure[id] = 0.f;
+  recB[2 * (size_t)id + 1] = zero;
+  spPred[id] = predict_position(d, pi, vi, zero);
+}
+
+// predictDensity + correctPressure (k_predict_density<true, .>)
+template <int L>
+__global__ void __launch_bounds__(LaneGeom<L>::T) k_predict_density_lanes(DevParams d, const float4 *__restrict__ spPred,
+                                                                      const int *__restrict__ nb, float *__restrict__ rho,
+                                                                      float *__restrict__ pressure,
+                                                                      float4 *__restrict__ recB) {
+  using G = LaneGeom<L>;
+  __shared__ float term[G::CS];
+  const int t = threadIdx.x, pl = t / L, l = t % L;
+  const int id = blockIdx.x * G::P + pl;
+  const bool live = id < d.N;
+  if (live) {
+    const float4 pi = spPred[id];
+    int jd[G::SLOTS];
+    float4 Pj[G::SLOTS];
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) jd[i] = __ldg(nb + nb_index(id, l + L * i));
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) Pj[i] = ldg4(spPred + (jd[i] != SPH_NO_ID ? jd[i] : id));
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) {
+      float w = 0.f;
+      if (jd[i] != SPH_NO_ID && !density_term(d, pi, Pj[i], w)) w = 0.f;
+      term[pl * G::S + l + L * i] = w;
+    }
+  }
+  __syncthreads();
+  if (!live || l != 0) return;
+  double density = 0.0;
+  const float *a = term + pl * G::S;
+#pragma unroll 8
+  for (int k = 0; k < SPH_NB; k++) density += (double)a[k];
+  if (density < (double)d.hScaled6) density = (double)d.hScaled6;
+  density *= d.massWpoly6;
+  const float rhoP = (float)density;
+  rho[d.N + id] = rhoP;
+  float p_corr = (rhoP - d.rho0) * d.delta;  // :1093-1096
+  if (p_corr < 0.f) p_corr = 0.f;
+  const float p = recB[2 * (size_t)id + 1].x + p_corr;
+  pressure[id] = p;
+  recB[2 * (size_t)id + 1] = f4(p, rhoP, 0.f, 0.f);
+}
+
+// computePressureForceAcceleration + predictPositions (MODE 1) or + integrate (MODE 2): k_pressure_force<MODE, .>
+template <int MODE, int L>
+__global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevParams d, const float4 *__restrict__ spT,
+                                                                     const float4 *__restrict__ sv,
+                                                                     const int *__restrict__ nb,
+                                                                     const float4 *__restrict__ recB,
+                                                                     float4 *__restrict__ acc, const float4 *__restrict__ sp,
+                                                                     float4 *__restrict__ spPred,
+                                                                     const uint2 *__restrict__ particleIndex,
+                                                                     float4 *__restrict__ position,
+                                                                     float4 *__restrict__ velocity,
+                                                                     unsigned *__restrict__ elasticMask) {
+  using G = LaneGeom<L>;
+  __shared__ float term[3 * G::CS];
+  const int t = threadIdx.x, pl = t / L, l = t % L;
+  const int id = blockIdx.x * G::P + pl;
+  const bool live = id < d.N;
+  float4 pi = f4(0.f, 0.f, 0.f, 0.f);
+  bool active = false;
+  if (live) {
+    pi = spT[id];
+    active = !is_boundary(pi.w);
+  }
+  float rho_i = 1.f;
+  unsigned bmask = 0, emask = 0;
+  if (active) {
+    const float4 ti = recB[2 * (size_t)id + 1];
+    const float p_i = ti.x;
+    rho_i = ti.y;
+    const float closeThr = (float)d.closeThr;
+    const float hq = d.hScaled * 0.25f;
+    int jd[G::SLOTS];
+    float4 Pj[G::SLOTS], Qj[G::SLOTS];
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) jd[i] = __ldg(nb + nb_index(id, l + L * i));
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) ld256(recB + 2 * (size_t)(jd[i] != SPH_NO_ID ? jd[i] : id), Pj[i], Qj[i]);
+#pragma unroll
+    for (int i = 0; i < G::SLOTS; i++) {
+      const int k = l + L * i;
+      float ax = 0.f, ay = 0.f, az = 0.f;
+      if (jd[i] != SPH_NO_ID) {
+        if (MODE == 2 && is_boundary(Pj[i].w)) bmask |= 1u << k;
+        if (MODE == 2 && (int)Pj[i].w == SPH_ELASTIC_PARTICLE) emask |= 1u << k;
+        if (!pressure_term(d, pi, p_i, Pj[i], Qj[i].x, Qj[i].y, closeThr, hq, ax, ay, az)) ax = ay = az = 0.f;
+      }
+      float *o = term + pl * G::S + k;
+      o[0] = ax; o[G::CS] = ay; o[2 * G::CS] = az;
+    }
+  }
+  __syncthreads();
+  float s = 0.f;
+  if (active && l < 3) {
+    const float *a = term + l * G::CS + pl * G::S;
+#pragma unroll 8
+    for (int k = 0; k < SPH_NB; k++) s += a[k];
+  }
+  const int base = (t & 31) - l;
+  const float rx = __shfl_sync(0xffffffffu, s, base), ry = __shfl_sync(0xffffffffu, s, base + 1),
+              rz = __shfl_sync(0xffffffffu, s, base + 2);
+  if (MODE == 2) {
+#pragma unroll
+    for (int o = 1; o < L; o <<= 1) {
+      bmask |= __shfl_xor_sync(0xffffffffu, bmask, o);
+      emask |= __shfl_xor_sync(0xffffffffu, emask, o);
+    }
+  }
+  if (!live || l != 0) return;
+  if (!active) {
+    acc[d.N + id] = f4(0.f, 0.f, 0.f, 0.f);  // :1126-1129
+    return;
+  }
+  const float cf = (float)(d.massGradW / (double)rho_i);  // :1194
+  const float4 result = f4(rx * cf, ry * cf, rz * cf, 0.f);
+  acc[d.N + id] = result;
+  if (MODE == 1) spPred[id] = predict_position(d, sp[id], sv[id], result);
+  if (MODE == 2 && elasticMask) elasticMask[id] = emask;
+  if (MODE == 2)
+    integrate_particle(d, id, sp[id], sv[id], acc[id] + result, pi.w, particleIndex[id].y, bmask, spT, sv, nb, position,
+                       velocity, /*foldFinalize=*/elasticMask == nullptr);
+}
+
+// ---------------------------------------------------------------- launchers
+template <int L> static inline int lanes_grid(int n) { return (n + LaneGeom<L>::P - 1) / LaneGeom<L>::P; }
+
+bool launch_forces_lanes(sph_ctx *c, int L) {
+  float4 *pred = c->sortedPosition + c->d.N;
+#define F_ARGS c->d, c->sortedPosition, c->sortedVelocity, c->sortedType, c->nbIds, c->rho, c->acceleration, c->pressure, pred, c->recA, c->recB
+  if (L == 4) k_forces_lanes<4><<<lanes_grid<4>(c->d.N), LaneGeom<4>::T, 0, c->stream>>>(F_ARGS);
+  else if (L == 8) k_forces_lanes<8><<<lanes_grid<8>(c->d.N), LaneGeom<8>::T, 0, c->stream>>>(F_ARGS);
+  else if (L == 16) k_forces_lanes<16><<<lanes_grid<16>(c->d.N), LaneGeom<16>::T, 0, c->stream>>>(F_ARGS);
+  else return false;
+#undef F_ARGS
+  return true;
+}
+
+bool launch_predict_density_lanes(sph_ctx *c, int L) {
+  const float4 *pred = c->sortedPosition + c->d.N;
+#define D_ARGS c->d, pred, c->nbIds, c->rho, c->pressure, c->recB
+  if (L == 4) k_predict_density_lanes<4><<<lanes_grid<4>(c->d.N), LaneGeom<4>::T, 0, c->stream>>>(D_ARGS);
+  else if (L == 8) k_predict_density_lanes<8><<<lanes_grid<8>(c->d.N), LaneGeom<8>::T, 0, c->stream>>>(D_ARGS);
+  else if (L == 16) k_predict_density_lanes<16><<<lanes_grid<16>(c->d.N), LaneGeom<16>::T, 0, c->stream>>>(D_ARGS);
+  else return false;
+#undef D_ARGS
+  return true;
+}
+
+bool launch_pressure_force_lanes(sph_ctx *c, int mode, int L) {
+  float4 *pred = c->sortedPosition + c->d.N;
+#define P_ARGS c->d, c->spT, c->sortedVelocity, c->nbIds, c->recB, c->acceleration, c->sortedPosition, pred, c->particleIndex, \
+               c->position, c->velocity, c->elasticMask
+#define P_LAUNCH(M, LL) k_pressure_force_lanes<M, LL><<<lanes_grid<LL>(c->d.N), LaneGeom<LL>::T, 0, c->stream>>>(P_ARGS)
+  if (mode != 1 && mode != 2) return false;
+  if (L == 4) { if (mode == 1) P_LAUNCH(1, 4); else P_LAUNCH(2, 4); }
+  else if (L == 8) { if (mode == 1) P_LAUNCH(1, 8); else P_LAUNCH(2, 8); }
+  else if (L == 16) { if (mode == 1) P_LAUNCH(1, 16); else P_LAUNCH(2, 16); }
+  else return false;
+#undef P_LAUNCH
+#undef P_ARGS
+  return true;
+}

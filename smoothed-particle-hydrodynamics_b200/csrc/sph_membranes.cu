@@ -48,16 +48,19 @@ __global__ void __launch_bounds__(256) k_clear_membrane_buffers(DevParams d, flo
   velocity[d.N + id] = f4(0.f, 0.f, 0.f, 0.f);
 }
 
-// One thread per sorted particle. FUSED: also clears the displacement slot and applies the
-// finalize step for this particle (legal: only liquid particles receive a displacement and no
-// other thread reads a liquid particle's position in this kernel).
+// One thread per sorted particle. FUSED: also clears the displacement slots (clearMembraneBuffers) and applies
+// the finalize step to LIQUID particles (legal: only liquid particles receive a displacement and no other thread
+// reads a liquid particle's position in this kernel). Elastic particles — whose positions other threads read here
+// as membrane vertices — are finalized by k_membrane_finalize_elastic afterwards: their displacement is +0, so
+// the add can only turn a -0 coordinate into +0, but it must not race with those reads.
 template <bool FUSED>
 __global__ void __launch_bounds__(128) k_membrane_interaction(DevParams d, float4 *__restrict__ position,
                                                               const uint2 *__restrict__ particleIndex,
                                                               const float *__restrict__ sortedType,
                                                               const int *__restrict__ nb, const int *__restrict__ pml,
                                                               const int *__restrict__ membraneData,
-                                                              const unsigned *__restrict__ elasticMask) {
+                                                              const unsigned *__restrict__ elasticMask,
+                                                              float4 *__restrict__ velocity) {
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= d.N) return;
   const int src = (int)particleIndex[id].y;
@@ -126,7 +129,8 @@ __global__ void __launch_bounds__(128) k_membrane_interaction(DevParams d, float
   }
   if (FUSED) {
     position[d.N + src] = disp;
-    if (type != SPH_BOUNDARY_PARTICLE) {  // finalize, :1670-1673
+    velocity[d.N + src] = f4(0.f, 0.f, 0.f, 0.f);  // clearMembraneBuffers, :1225
+    if (type == SPH_LIQUID_PARTICLE) {  // finalize, :1670-1673
       float4 p = position[src];
       float4 q = p + disp;
       if (__float_as_uint(q.x) != __float_as_uint(p.x) || __float_as_uint(q.y) != __float_as_uint(p.y) ||
@@ -148,18 +152,36 @@ __global__ void __launch_bounds__(256) k_membrane_finalize(DevParams d, float4 *
   position[src] = position[src] + position[d.N + src];
 }
 
+// finalize (:1670-1673) of the fused path for everything that is neither liquid (done in the interaction kernel)
+// nor boundary (never finalized): the elastic matter
+__global__ void __launch_bounds__(256) k_membrane_finalize_elastic(DevParams d, float4 *__restrict__ position,
+                                                                   const uint2 *__restrict__ particleIndex,
+                                                                   const float *__restrict__ sortedType) {
+  int id = blockIdx.x * blockDim.x + threadIdx.x;
+  if (id >= d.N) return;
+  const int type = (int)sortedType[id];
+  if (type == SPH_BOUNDARY_PARTICLE || type == SPH_LIQUID_PARTICLE) return;
+  const int src = (int)particleIndex[id].y;
+  const float4 p = position[src];
+  const float4 q = p + position[d.N + src];
+  if (__float_as_uint(q.x) != __float_as_uint(p.x) || __float_as_uint(q.y) != __float_as_uint(p.y) ||
+      __float_as_uint(q.z) != __float_as_uint(p.z) || __float_as_uint(q.w) != __float_as_uint(p.w))
+    position[src] = q;
+}
+
 void launch_clear_membrane_buffers(sph_ctx *c) {
   k_clear_membrane_buffers<<<(c->d.N + 255) / 256, 256, 0, c->stream>>>(c->d, c->position, c->velocity);
 }
 
 void launch_membrane_interaction(sph_ctx *c, bool fuse_finalize) {
   const int *pml = c->has_pml ? c->pml : nullptr;
-  if (fuse_finalize)
+  if (fuse_finalize) {
     k_membrane_interaction<true><<<(c->d.N + 127) / 128, 128, 0, c->stream>>>(c->d, c->position, c->particleIndex,
-                                                                            c->sortedType, c->nbIds, pml, c->membraneData, c->elasticMask);
-  else
+                                                                            c->sortedType, c->nbIds, pml, c->membraneData, c->elasticMask, c->velocity);
+    k_membrane_finalize_elastic<<<(c->d.N + 255) / 256, 256, 0, c->stream>>>(c->d, c->position, c->particleIndex, c->sortedType);
+  } else
     k_membrane_interaction<false><<<(c->d.N + 127) / 128, 128, 0, c->stream>>>(c->d, c->position, c->particleIndex,
-                                                                             c->sortedType, c->nbIds, pml, c->membraneData, nullptr);
+                                                                             c->sortedType, c->nbIds, pml, c->membraneData, nullptr, c->velocity);
 }
 
 void launch_membrane_finalize(sph_ctx *c) {

@@ -518,6 +518,219 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   }
 }
 
+// ---------------------------------------------------------------- cooperative path (small scenes)
+// EIGHT LANES PER PARTICLE, for scenes that do not fill the GPU with one thread per particle (the reference's own
+// 61 k / 233 k particle scenes): there the list kernel lasts as long as ONE thread's walk over ~500-800 candidates
+// and ~40-60 dependent gathers. Here the candidate sequence of a particle — its 8 cells in the reference's visiting
+// order, cut into aligned groups of 16 — is dealt round-robin to the 8 lanes:
+//   sweep   round r: lane l filters group 8r + l with the fp16 test of the list kernel; a prefix sum of the hit
+//           counts over the 8 lanes (groups of a round are in scan order) places every hit at its scan-order
+//           position in the particle's list in shared memory: one pass, ordered output;
+//   select  lane l re-evaluates hits l, l + 8, ... exactly (fp32, reference operation order), the 8 partial radial
+//           histograms are added with shuffles, every lane derives r_thr, and the "first 32 within r_thr" of
+//           sphFluid.cl:166-174 is a ballot + prefix popcount over the hits in list order;
+//   rho(t)  the terms of the selected neighbours go to shared memory by slot, lane 0 adds them in slot order (fp64).
+// A particle with more than CP_CAP hits or a cell of more than 8191 particles takes find_neighbors_one (lane 0).
+#ifndef SPH_COOP_MAX_N
+#define SPH_COOP_MAX_N (1 << 18)
+#endif
+#define CP_L 8
+#define CP_THREADS 256
+#define CP_P (CP_THREADS / CP_L)
+#define CP_CAP 128
+
+template <bool WITH_DENSITY>
+__global__ void __launch_bounds__(CP_THREADS) k_find_neighbors_coop(DevParams d, const float4 *__restrict__ sp,
+                                                                    const float *__restrict__ S,
+                                                                    const unsigned *__restrict__ cellStart,
+                                                                    int *__restrict__ nb, float *__restrict__ rho,
+                                                                    float4 *__restrict__ recA) {
+  __shared__ int hitJ[CP_P][CP_CAP + 1];      // sorted index of hit t (odd row stride)
+  __shared__ float hitD[CP_P][CP_CAP + 1];    // its exact squared distance
+  __shared__ float rhoT[CP_P][SPH_NB + 1];    // rho(t) term of the neighbour in slot s
+  const int t = threadIdx.x, pl = t / CP_L, l = t % CP_L;
+  const int id = blockIdx.x * CP_P + pl;
+  const bool live = id < d.N;
+  const int gshift = (t & 31) - l;            // first lane of this particle's group inside the warp
+  const float4 pos = sp[live ? id : 0];
+  const int myCell = (int)pos.w & d.mask;
+  int cells[8];
+  neighbor_cells(d, pos, myCell, cells);
+  int cb[8], ce[8], ng[8];                    // first / end index, number of aligned 16-groups per visited cell
+  int total = 0;
+  bool fits = true;
+#pragma unroll
+  for (int k = 0; k < 8; k++) {
+    const int b = (int)cellStart[cells[k]], e = (int)cellStart[cells[k] + 1];
+    cb[k] = b;
+    ce[k] = e;
+    ng[k] = e > b ? ((e + 15) >> 4) - (b >> 4) : 0;
+    total += ng[k];
+    fits = fits && (e - b < 8192);
+  }
+  // sweep
+  const float3 up = cell_local_h(d, pos, 1.0f / d.h);
+  const float sgx = (((pos.x - d.xmin) - (float)(int)(pos.x * d.cellSizeInv) * d.cellSize) < d.h) ? -2.0f : 2.0f;
+  const float sgy = (((pos.y - d.ymin) - (float)(int)(pos.y * d.cellSizeInv) * d.cellSize) < d.h) ? -2.0f : 2.0f;
+  const float sgz = (((pos.z - d.zmin) - (float)(int)(pos.z * d.cellSizeInv) * d.cellSize) < d.h) ? -2.0f : 2.0f;
+  const __half2 nT = __float2half2_rn(-1.08984375f);  // see k_find_neighbors_list
+  const __half *Sh = reinterpret_cast<const __half *>(S);
+  int n = 0;
+  const int rounds = (live && fits) ? (total + CP_L - 1) / CP_L : 0;
+  // every lane of the warp runs the same number of rounds (shuffles inside): the maximum over the 4 particles
+  int wrounds = rounds;
+#pragma unroll
+  for (int o = CP_L; o < 32; o <<= 1) wrounds = max(wrounds, __shfl_xor_sync(0xffffffffu, wrounds, o));
+#pragma unroll 1
+  for (int r = 0; r < wrounds; r++) {
+    const int g = r * CP_L + l;
+    unsigned m = 0u;
+    int j0 = 0;
+    if (r < rounds && g < total) {
+      int k = 0, gl = g;                     // visited cell of group g and the group's index inside it
+#pragma unroll
+      for (int q = 0; q < 7; q++) {
+        const bool next = (k == q) && gl >= ng[q];
+        gl -= next ? ng[q] : 0;
+        k += next ? 1 : 0;
+      }
+      int b = cb[0], e = ce[0];
+#pragma unroll
+      for (int q = 1; q < 8; q++) { b = (k == q) ? cb[q] : b; e = (k == q) ? ce[q] : e; }
+      j0 = (b & ~15) + 16 * gl;
+      const __half2 px = __float2half2_rn(up.x - (((0xB2 >> k) & 1) ? sgx : 0.0f));
+      const __half2 py = __float2half2_rn(up.y - (((0xD4 >> k) & 1) ? sgy : 0.0f));
+      const __half2 pz = __float2half2_rn(up.z - (((0xE8 >> k) & 1) ? sgz : 0.0f));
+      uint4 xa, xb, ya, yb, za, zb;
+      const __half *gp = Sh + 3 * (size_t)j0;
+      ld256u(gp, xa, xb);
+      ld256u(gp + 16, ya, yb);
+      ld256u(gp + 32, za, zb);
+      auto lane2 = [&](unsigned x, unsigned y, unsigned z, int rr) {
+        const __half2 ex = __hsub2(*reinterpret_cast<const __half2 *>(&x), px);
+        const __half2 ey = __hsub2(*reinterpret_cast<const __half2 *>(&y), py);
+        const __half2 ez = __hsub2(*reinterpret_cast<const __half2 *>(&z), pz);
+        const __half2 a = __hfma2(ez, ez, __hfma2(ey, ey, __hfma2(ex, ex, nT)));  // d2 - T: negative = hit
+        m |= ((*reinterpret_cast<const unsigned *>(&a)) >> (15 - rr)) & (0x00010001u << rr);
+      };
+      lane2(xa.x, ya.x, za.x, 0); lane2(xa.y, ya.y, za.y, 1); lane2(xa.z, ya.z, za.z, 2); lane2(xa.w, ya.w, za.w, 3);
+      lane2(xb.x, yb.x, zb.x, 4); lane2(xb.y, yb.y, zb.y, 5); lane2(xb.z, yb.z, zb.z, 6); lane2(xb.w, yb.w, zb.w, 7);
+      // bits 0-7 = candidates j0..j0+7, bits 16-23 = candidates j0+8..j0+15: fold into 16 ascending bits
+      m = (m & 0xffu) | ((m >> 8) & 0xff00u);
+      // the group is aligned to 16: its ends may reach into the neighbouring cells
+      m &= (0xffffu << max(b - j0, 0)) & (0xffffu >> max(j0 + 16 - e, 0));
+    }
+    // scan-order position of this lane's hits: hits of the lanes before it in this round come first
+    const int cnt = __popc(m);
+    int inc = cnt;
+#pragma unroll
+    for (int o = 1; o < CP_L; o <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, inc, o);
+      if (l >= o) inc += u;
+    }
+    int at = n + inc - cnt;
+    n += __shfl_sync(0xffffffffu, inc, gshift + CP_L - 1);
+    while (m) {
+      const int i = __ffs(m) - 1;
+      m &= m - 1u;
+      if (at < CP_CAP) hitJ[pl][at] = j0 + i;
+      at++;
+    }
+  }
+  __syncwarp();
+  const bool generic = live && (!fits || n > CP_CAP);
+  if (generic) {
+    if (l == 0) find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
+    n = 0;
+  }
+  const bool work = live && !generic;
+  // exact distances and the radial histogram (30 bins x 7 bits, as in the list kernel)
+  unsigned long long hist0 = 0ull, hist1 = 0ull, hist2 = 0ull, hist3 = 0ull;
+  const float h2 = d.h * d.h;
+#pragma unroll 1
+  for (int q = l; q < n; q += CP_L) {
+    const int j = hitJ[pl][q];
+    const float4 c = ldg4(sp + j);
+    const float ex = pos.x - c.x, ey = pos.y - c.y, ez = pos.z - c.z;
+    const float dd = ex * ex + ey * ey + ez * ez;
+    hitD[pl][q] = dd;
+    if (j != id && dd <= h2) {
+      float sq;
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
+      const int e = min((int)(sq * d.binScale), SPH_RADIUS_SEGMENTS);
+      const int bin = e + ((dd >= d.binT[e + 1]) ? 1 : 0) - ((dd < d.binT[e]) ? 1 : 0);
+      if (bin < SPH_RADIUS_SEGMENTS) {
+        const int w = bin >> 3;
+        const unsigned long long inc = 1ull << ((bin & 7) * 7);
+        hist0 += (w == 0) ? inc : 0ull;
+        hist1 += (w == 1) ? inc : 0ull;
+        hist2 += (w == 2) ? inc : 0ull;
+        hist3 += (w == 3) ? inc : 0ull;
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 1; o < CP_L; o <<= 1) {  // at most CP_CAP - 1 = 127 other particles: no 7-bit bin can overflow
+    hist0 += __shfl_xor_sync(0xffffffffu, hist0, o);
+    hist1 += __shfl_xor_sync(0xffffffffu, hist1, o);
+    hist2 += __shfl_xor_sync(0xffffffffu, hist2, o);
+    hist3 += __shfl_xor_sync(0xffffffffu, hist3, o);
+  }
+  int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
+  {
+    int sum = 0;
+    bool open = true;
+#pragma unroll
+    for (int jj = 0; jj < SPH_RADIUS_SEGMENTS; jj++) {
+      const unsigned long long hw = jj < 8 ? hist0 : (jj < 16 ? hist1 : (jj < 24 ? hist2 : hist3));
+      sum += (int)((hw >> ((jj & 7) * 7)) & 127ull);
+      if (open && sum >= SPH_NB) { jthr = (sum == SPH_NB) ? jj : jj - 1; open = false; }
+    }
+  }
+  const float r_thr = (float)(jthr + 1) * d.h / SPH_RADIUS_SEGMENTS;
+  const float r2 = r_thr * r_thr;
+  // first 32 within r_thr, in list (= scan) order
+  int found = 0;
+  int wn = n;
+#pragma unroll
+  for (int o = CP_L; o < 32; o <<= 1) wn = max(wn, __shfl_xor_sync(0xffffffffu, wn, o));
+#pragma unroll 1
+  for (int q0 = 0; q0 < wn; q0 += CP_L) {
+    const int q = q0 + l;
+    bool take = false;
+    int j = 0;
+    float dd = 0.f;
+    if (q < n) {
+      j = hitJ[pl][q];
+      dd = hitD[pl][q];
+      take = (j != id) && (dd <= r2);
+    }
+    const unsigned bits = (__ballot_sync(0xffffffffu, take) >> gshift) & ((1u << CP_L) - 1u);
+    const int slot = found + __popc(bits & ((1u << l) - 1u));
+    if (take && slot < SPH_NB) {
+      nb[nb_index(id, slot)] = j;
+      if (WITH_DENSITY) {  // pcisph_computeDensity term, sphFluid.cl:505-507
+        const float rr0 = sqrtf(dd) * d.simScale;
+        const float rr = rr0 * rr0;
+        rhoT[pl][slot] = (d.hScaled2 - rr) * (d.hScaled2 - rr) * (d.hScaled2 - rr);
+      }
+    }
+    found += __popc(bits);
+  }
+  __syncwarp();
+  if (!work) return;
+  found = min(found, SPH_NB);
+  for (int k = found + l; k < SPH_NB; k += CP_L) nb[nb_index(id, k)] = SPH_NO_ID;
+  if (WITH_DENSITY && l == 0) {  // sphFluid.cl:514-517
+    double density = 0.0;
+    for (int k = 0; k < found; k++) density += (double)rhoT[pl][k];
+    if (density < (double)d.hScaled6) density = (double)d.hScaled6;
+    density *= d.massWpoly6;
+    rho[id] = (float)density;
+    if (recA) reinterpret_cast<float *>(recA)[8 * (size_t)id + 7] = (float)density;
+  }
+}
+
 // ---------------------------------------------------------------- tiled path (round-1 design, superseded by the list
 // path above; kept as an independent implementation for the parity tests and A/B runs: SPH_NEIGHBOR_PATH=tiles|auto)
 // One persistent kernel, k_neighbor_tiles. A CTA takes a HOME BLOCK = the two hash cells (2b, 2b+1),
@@ -1080,6 +1293,16 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
       k_soa_positions_half<<<(n + 32 + 255) / 256, 256, 0, c->stream>>>(c->d, c->sortedPosition, reinterpret_cast<__half *>(c->soa));
     else
       k_soa_positions<<<(n + 16 + 255) / 256, 256, 0, c->stream>>>(n, c->sortedPosition, c->soa);
+    // small scenes: eight lanes per particle (SPH_NEIGHBOR_PATH=coop forces it at any size, =list forbids it)
+    const bool coop = var == 2 && (c->force_coop_neighbors || (!c->force_list_neighbors && n <= SPH_COOP_MAX_N));
+    if (coop) {
+      const int cb = (n + CP_P - 1) / CP_P;
+      if (with_density)
+        k_find_neighbors_coop<true><<<cb, CP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, c->rho, c->recA);
+      else
+        k_find_neighbors_coop<false><<<cb, CP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, c->rho, nullptr);
+      return;
+    }
     const int blocks = (n + LP_THREADS - 1) / LP_THREADS;
 #define LP_LAUNCH(WD, V, REC)                                                                                      \
   k_find_neighbors_list<WD, V><<<blocks, LP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, \

@@ -24,8 +24,14 @@
 template <bool WRITE_PAIRS>
 __global__ void __launch_bounds__(256) k_hash_count(DevParams d, const float4 *__restrict__ position,
                                                     unsigned *__restrict__ key, unsigned *__restrict__ cellCount,
-                                                    uint2 *__restrict__ particleIndex) {
+                                                    uint2 *__restrict__ particleIndex,
+                                                    unsigned long long *__restrict__ scanState,
+                                                    unsigned *__restrict__ scanTicket, int scanTiles) {
   int id = blockIdx.x * blockDim.x + threadIdx.x;
+  // reset the look-back scan of this step's sort (k_scan_cells runs after this kernel): the step's launch
+  // parameters are then the same every step, which is what lets sph_step replay a captured CUDA graph
+  for (int t = id; t < scanTiles; t += gridDim.x * blockDim.x) scanState[t] = 0ull;
+  if (id == 0) *scanTicket = 0u;
   if (id >= d.N) return;
   float4 p = position[id];
   // cellFactors: no xmin subtraction (sphFluid.cl:197-199); cellId (:339-340); low-bit mask (:377)
@@ -220,17 +226,18 @@ void launch_hash_count(sph_ctx *c, bool write_pairs) {
   const int N = c->d.N;
   cudaMemsetAsync(c->cellCount, 0, sizeof(unsigned) * ((size_t)c->d.G + 1), c->stream);
   if (write_pairs)
-    k_hash_count<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex);
+    k_hash_count<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex,
+                                                                  c->scanState, c->scanTicket, c->scanTiles);
   else
-    k_hash_count<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex);
+    k_hash_count<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex,
+                                                                   c->scanState, c->scanTicket, c->scanTiles);
 }
 
 void launch_sort(sph_ctx *c, bool fuse_reorder) {
   const int N = c->d.N, n = c->d.G + 1;
-  c->epoch++;
-  unsigned ticketBase = (c->epoch - 1u) * (unsigned)c->scanTiles;
+  // scan state and ticket were zeroed by k_hash_count: constant epoch, no per-step launch parameter
   k_scan_cells<<<c->scanTiles, SCAN_THREADS, 0, c->stream>>>(c->cellCount, c->cellStart, n, c->scanState, c->scanTicket,
-                                                             ticketBase, c->epoch, c->cellListCount);
+                                                             0u, 1u, c->cellListCount);
   k_scatter<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->cellCount, c->tmpSerial, c->rankKey,
                                                        c->tmpRankKey);
   const unsigned *rk = c->rankKey ? c->tmpRankKey : nullptr;

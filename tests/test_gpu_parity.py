@@ -38,17 +38,31 @@ STAGE_OUTPUTS = {
 }
 
 
-@pytest.fixture(scope="module", autouse=True, params=["tiles", "generic", "list"])
+# every parity test runs once per row: neighbour-search path x lanes per particle of the gather kernels x CUDA graph
+VARIANTS = {
+    "tiles": dict(SPH_NEIGHBOR_PATH="tiles", SPH_LANES="1", SPH_GRAPH="0"),
+    "generic-lanes4": dict(SPH_NEIGHBOR_PATH="generic", SPH_LANES="4", SPH_GRAPH="0"),
+    "list-lanes16-graph": dict(SPH_NEIGHBOR_PATH="list", SPH_LANES="16", SPH_GRAPH="1"),
+    "coop-lanes8-graph": dict(SPH_NEIGHBOR_PATH="coop", SPH_LANES="8", SPH_GRAPH="1"),
+    "default": dict(),   # what the library picks by size: the product path
+}
+
+
+@pytest.fixture(scope="module", autouse=True, params=list(VARIANTS))
 def neighbor_path(request):
-    """Every parity test runs twice: with the tile kernel forced (the path large fluids take; the test scenes are
-    below the size where the library picks it by itself) and with the one-thread-per-particle scan."""
-    old = os.environ.get("SPH_NEIGHBOR_PATH")
-    os.environ["SPH_NEIGHBOR_PATH"] = request.param
+    """Force the independent implementations of the step's kernels through their environment switches (read at
+    sph_create): the tile / plain / list / cooperative neighbour search, 1 / 4 / 8 / 16 lanes per particle in the
+    gather kernels, eager launches or the captured CUDA graph."""
+    keys = ["SPH_NEIGHBOR_PATH", "SPH_LANES", "SPH_GRAPH"]
+    old = {k: os.environ.get(k) for k in keys}
+    for k in keys:
+        os.environ.pop(k, None)
+    os.environ.update(VARIANTS[request.param])
     yield request.param
-    if old is None:
-        os.environ.pop("SPH_NEIGHBOR_PATH", None)
-    else:
-        os.environ["SPH_NEIGHBOR_PATH"] = old
+    for k in keys:
+        os.environ.pop(k, None)
+        if old[k] is not None:
+            os.environ[k] = old[k]
 
 
 @pytest.fixture(scope="module")
