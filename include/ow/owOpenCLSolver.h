@@ -33,6 +33,7 @@ class owOpenCLSolver {
  public:
   owOpenCLSolver(const float *position_cpp, const float *velocity_cpp, const float *elasticConnectionsData_cpp = 0,
                  const int *membraneData_cpp = 0, const int *particleMembranesList_cpp = 0);
+  owOpenCLSolver(void);  // declared (never defined) by the reference, owOpenCLSolver.h:32: an empty solver, no device buffers
   ~owOpenCLSolver(void);
   // neighbour search (owOpenCLSolver.h:37-43)
   unsigned int _runClearBuffers();
@@ -62,11 +63,17 @@ class owOpenCLSolver {
   // ---- additions (no reference counterpart) ----
   unsigned int _runFusedStep();       // the 18 stages above as one fused launch sequence, same results
   void read_velocity_buffer(float *velocity_cpp);
+  // run-ahead support (owPhysicsFluidSimulator queues step k+1 before simulationStep k returns):
+  void read_position_begin(float *pinned_position_cpp);  // read_position_buffer without its blocking wait ...
+  void read_position_end();                              // ... which happens here
+  void snapshot(bool with_velocity); // freeze rho / particleIndex (/ velocity) of the step queued so far for the read_* methods
+  void setReadFromSnapshot(bool on) { fromSnapshot = on; }
   sph_ctx *context() { return ctx; }
 
  private:
   unsigned int stage(int id);
   sph_ctx *ctx;
+  bool fromSnapshot;
 };
 
 #endif  // OW_OPENCL_SOLVER_H

@@ -191,6 +191,9 @@ const char *sph_backend(void);
 /* Run `steps` fused steps and return the device time in ms, measured with CUDA events on the
  * context's own stream with a synchronize on both sides. */
 int sph_run_steps(sph_ctx *ctx, int steps, float *elapsed_ms);
+/* Device timer (CUDA events on the context's stream, synchronize on both sides) around work the caller queues itself. */
+int sph_timer_start(sph_ctx *ctx);
+int sph_timer_stop(sph_ctx *ctx, float *elapsed_ms);
 /* Per-kernel CUDA-event timing of sph_step on/off; report = JSON {"kernel": {"calls":n,"ms":t}}. */
 int sph_profile_enable(sph_ctx *ctx, int on);
 int sph_profile_report(sph_ctx *ctx, char *buf, size_t n);
@@ -234,6 +237,26 @@ int sph_slab_set_cut(sph_ctx *ctx, int z0, int z1);
 /* Pipelined form for the owned positions (pinned pos4): overlaps the next step; complete it with sph_read_end. */
 int sph_slab_read_owned_begin(sph_ctx *ctx, float *pos4);
 const char *sph_slab_last_error(void);
+/* ---- links: halo exchange through PEER MEMORY (NVLink / NVSwitch P2P; north_star: "ghost-particle halos exchanged
+ * by NCCL (or P2P) over NVLink each step"). Every rank owns a mailbox in device memory that its two neighbours map
+ * (CUDA IPC between processes, peer access inside one process); their kernels store migrants, ghost layers, halo
+ * values and delivery flags straight into it, and the consuming kernels wait on the flags. With links set up,
+ * sph_slab_step runs a whole step — classify, exchange, absorb, the five parts and the six halo refreshes — with ONE
+ * host synchronisation (the particle counts after migration size the launches) and no call into NCCL or the host
+ * on the data path. ---- */
+int sph_slab_link_handle_bytes(void);
+/* Create this rank's mailbox; handle (may be NULL) receives its CUDA IPC handle for neighbours in other processes. */
+int sph_slab_link_export(sph_ctx *ctx, void *handle);
+/* Map the mailbox of the neighbour on `side` (0 = rank-1, 1 = rank+1): exported by another process / living in this one. */
+int sph_slab_link_open(sph_ctx *ctx, int side, const void *handle);
+int sph_slab_link_local(sph_ctx *ctx, int side, sph_ctx *peer);
+/* One step. A process that drives several ranks calls _begin on all of them, then _end on all of them (_end waits for
+ * the neighbours' deliveries); a process with one rank calls sph_slab_step. */
+int sph_slab_step_begin(sph_ctx *ctx);
+int sph_slab_step_end(sph_ctx *ctx);
+int sph_slab_step(sph_ctx *ctx);
+/* {migrants down, ghosts down, migrants up, ghosts up} sent in the last step. */
+int sph_slab_counts(const sph_ctx *ctx, int out[4]);
 /* The fused step in the five pieces between which a slab rank refreshes its ghosts:
  * 0 | rho | 1 | (p,rho*) | 2 | x* | 3 | (p,rho*) | 2 | x* | 3 | (p,rho*) | 4   for max_iteration = 3. */
 int sph_step_part(sph_ctx *ctx, int part);
@@ -245,6 +268,13 @@ int sph_set_stream(sph_ctx *ctx, void *cuda_stream);
  * sph_read_end blocks until the bytes have arrived. One read in flight per context. */
 int sph_read_begin(sph_ctx *ctx, int buffer_id, void *dst, size_t bytes);
 int sph_read_end(sph_ctx *ctx);
+/* For a caller that runs one step ahead (the drop-in owPhysicsFluidSimulator queues step k+1 before
+ * simulationStep k returns): sph_snapshot copies rho(t) and particleIndex (and, if asked, the first N rows of
+ * velocity) device-to-device in stream order; sph_read_snapshot(SPH_BUF_RHO | SPH_BUF_PARTICLE_INDEX |
+ * SPH_BUF_VELOCITY) is read_density_buffer / read_particleIndex_buffer
+ * (owOpenCLSolver.h:61-62) on that copy: blocking, but it does not wait for work queued after the snapshot. */
+int sph_snapshot(sph_ctx *ctx, int with_velocity);
+int sph_read_snapshot(sph_ctx *ctx, int buffer_id, void *dst, size_t bytes);
 /* Raw device memory for exchange buffers; synchronous copy between any host / device pointers. */
 void *sph_device_alloc(size_t bytes);
 void sph_device_free(void *p);

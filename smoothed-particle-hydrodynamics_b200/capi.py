@@ -113,6 +113,8 @@ class SphLib:
             L.sph_host_alloc.restype = C.c_void_p
             L.sph_host_free.argtypes = [C.c_void_p]
             L.sph_host_free.restype = None
+            L.sph_timer_start.argtypes = [C.c_void_p]
+            L.sph_timer_stop.argtypes = [C.c_void_p, P(C.c_float)]
 
     @property
     def backend(self):
@@ -203,6 +205,15 @@ class SphContext:
         """K fused steps timed on the device (CUDA events on the context's stream); returns ms."""
         ms = C.c_float(0)
         self.L.check(self.L.lib.sph_run_steps(self.h, int(steps), C.byref(ms)), "sph_run_steps")
+        return float(ms.value)
+
+    def stream_timer_start(self):
+        self.L.check(self.L.lib.sph_timer_start(self.h), "sph_timer_start")
+        return True
+
+    def stream_timer_stop(self, _token=None):
+        ms = C.c_float(0)
+        self.L.check(self.L.lib.sph_timer_stop(self.h, C.byref(ms)), "sph_timer_stop")
         return float(ms.value)
 
     def profile(self, on):

@@ -140,6 +140,21 @@ static void fill_dev_params(sph_ctx *c) {
   }
   { uint32_t inf = 0x7f800000u; memcpy(&d.binT[SPH_RADIUS_SEGMENTS + 1], &inf, 4); }
   d.binScale = (float)SPH_RADIUS_SEGMENTS / d.h;
+  // smallest float d2 with sqrtf(d2) * simScale >= limit (see DevParams::d2H)
+  auto d2_threshold = [&](float limit) -> float {
+    uint32_t lo = 0u, hi = 0x7f800000u;  // f(+0) = 0 < limit (limits are positive), f(+inf) = +inf >= limit
+    if (!(limit > 0.f)) return 0.f;
+    while (hi - lo > 1u) {
+      uint32_t mid = lo + (hi - lo) / 2u;
+      float f; memcpy(&f, &mid, 4);
+      volatile float r = sqrtf(f) * d.simScale;
+      if (r >= limit) hi = mid; else lo = mid;
+    }
+    float out; memcpy(&out, &hi, 4);
+    return out;
+  };
+  d.d2H = d2_threshold(d.hScaled);
+  d.d2Close = d2_threshold((float)d.closeThr);
 }
 
 template <class T>
@@ -183,6 +198,9 @@ void sph_destroy(sph_ctx *c) {
     cudaFreeHost(c->hostDeferred);
     cudaEventDestroy(c->evDeferred);
   }
+  if (c->snapRho) { cudaFree(c->snapRho); cudaFree(c->snapIndex); cudaEventDestroy(c->evSnap); }
+  if (c->snapVel) cudaFree(c->snapVel);
+  if (c->evTimer[0]) { cudaEventDestroy(c->evTimer[0]); cudaEventDestroy(c->evTimer[1]); }
   if (c->sigRing) {
     cudaFreeHost(c->sigRing);
     for (cudaEvent_t e : c->sigDone) cudaEventDestroy(e);
@@ -583,6 +601,25 @@ int sph_run_steps(sph_ctx *c, int steps, float *elapsed_ms) {
   return 0;
 }
 
+// Device timer on the context's stream for work the caller queues itself (slab steps): start synchronises and
+// records, stop records, synchronises and returns the milliseconds in between.
+int sph_timer_start(sph_ctx *c) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  CU(cudaSetDevice(c->device));
+  if (!c->evTimer[0]) { CU(cudaEventCreate(&c->evTimer[0])); CU(cudaEventCreate(&c->evTimer[1])); }
+  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaEventRecord(c->evTimer[0], c->stream));
+  return 0;
+}
+int sph_timer_stop(sph_ctx *c, float *elapsed_ms) {
+  if (!c || !elapsed_ms || !c->evTimer[0]) return fail(SPH_E_INVALID, "sph_timer_stop");
+  CU(cudaSetDevice(c->device));
+  CU(cudaEventRecord(c->evTimer[1], c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaEventElapsedTime(elapsed_ms, c->evTimer[0], c->evTimer[1]));
+  return 0;
+}
+
 long long sph_launch_count(const sph_ctx *c) { return c ? c->launches : 0; }
 
 // Pinned host memory for the read-back / upload buffers of the e2e path.
@@ -709,6 +746,61 @@ int sph_read_end(sph_ctx *c) {
   CU(cudaSetDevice(c->device));
   CU(cudaEventSynchronize(c->evReadDone));
   c->readPending = 0;
+  return 0;
+}
+
+// ---- state snapshot for a caller that runs one step ahead (the drop-in owPhysicsFluidSimulator launches step
+// k+1 before simulationStep k returns): rho(t) and particleIndex of the step just queued are copied device-to-
+// device in stream order, so that getDensity_cpp / getParticleIndex_cpp can still deliver step k while step k+1
+// overwrites the live buffers. 12 bytes per particle at HBM speed.
+static int ensure_copy_stream(sph_ctx *c) {
+  if (!c->copyStream) {
+    CU(cudaStreamCreateWithFlags(&c->copyStream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&c->evReadReady, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&c->evReadDone, cudaEventDisableTiming));
+  }
+  return 0;
+}
+
+int sph_snapshot(sph_ctx *c, int with_velocity) {
+  if (!c) return fail(SPH_E_INVALID, "null ctx");
+  CU(cudaSetDevice(c->device));
+  const size_t N = c->d.N;
+  if (!c->snapRho) {
+    CU(cudaMalloc((void **)&c->snapRho, 4 * N));
+    CU(cudaMalloc((void **)&c->snapIndex, 8 * N));
+    CU(cudaEventCreateWithFlags(&c->evSnap, cudaEventDisableTiming));
+  }
+  CU(cudaMemcpyAsync(c->snapRho, c->rho, 4 * N, cudaMemcpyDeviceToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->snapIndex, c->particleIndex, 8 * N, cudaMemcpyDeviceToDevice, c->stream));
+  if (with_velocity) {
+    if (!c->snapVel) CU(cudaMalloc((void **)&c->snapVel, 16 * N));
+    CU(cudaMemcpyAsync(c->snapVel, c->velocity, 16 * N, cudaMemcpyDeviceToDevice, c->stream));
+  }
+  CU(cudaEventRecord(c->evSnap, c->stream));
+  return 0;
+}
+
+// Blocking read of the last snapshot (SPH_BUF_RHO: first N floats; SPH_BUF_PARTICLE_INDEX); does not wait for
+// work queued after sph_snapshot.
+int sph_read_snapshot(sph_ctx *c, int id, void *dst, size_t bytes) {
+  if (!c || !dst) return fail(SPH_E_INVALID, "sph_read_snapshot: null");
+  if (!c->snapRho) return fail(SPH_E_INVALID, "sph_read_snapshot: no snapshot taken");
+  const size_t N = c->d.N;
+  const void *src;
+  size_t have;
+  if (id == SPH_BUF_RHO) { src = c->snapRho; have = 4 * N; }
+  else if (id == SPH_BUF_PARTICLE_INDEX) { src = c->snapIndex; have = 8 * N; }
+  else if (id == SPH_BUF_VELOCITY && c->snapVel) { src = c->snapVel; have = 16 * N; }
+  else return fail(SPH_E_UNSUPPORTED, "sph_read_snapshot: rho, particleIndex or (if requested) velocity only");
+  if (bytes > have) return fail(SPH_E_SIZE, "sph_read_snapshot: too many bytes");
+  CU(cudaSetDevice(c->device));
+  int rc = ensure_copy_stream(c);
+  if (rc) return rc;
+  if (c->readPending) return fail(SPH_E_INVALID, "sph_read_snapshot: a pipelined read is in flight");
+  CU(cudaStreamWaitEvent(c->copyStream, c->evSnap, 0));
+  CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->copyStream));
+  CU(cudaStreamSynchronize(c->copyStream));
   return 0;
 }
 

@@ -85,6 +85,11 @@ struct sph_ctx {
   cudaEvent_t evReadReady, evReadDone;
   int readPending;
   const void *readSrc;         // device buffer the pending read copies from
+  float *snapRho;              // sph_snapshot: rho(t) and particleIndex of the last completed step
+  uint2 *snapIndex;
+  float4 *snapVel;             // only when the caller asked for it
+  cudaEvent_t evSnap;
+  cudaEvent_t evTimer[2];      // sph_timer_start / sph_timer_stop
   // muscle signal upload: staged through a small pinned ring so that sph_set_muscles neither waits for the
   // step in flight nor depends on the caller's buffer after it returns
   float *sigRing;

@@ -42,6 +42,10 @@ struct DevParams {
   // binT[31] = +inf. The bin of d2 is then max{j : binT[j] <= d2}, exactly, without sqrt/div per candidate.
   float binT[SPH_RADIUS_SEGMENTS + 2];
   float binScale;                     // 30/h, for the approximate first guess of the bin
+  // r_ij = sqrtf(d2) * simulationScale is a monotone function of d2, so the two range tests of the pressure force
+  // (sphFluid.cl:1150, :1166) are tests on d2 against host-built thresholds (bisection over float bit patterns with
+  // the same IEEE operations): r_ij < hScaled <=> d2 < d2H, r_ij < closeThr <=> d2 < d2Close. No sqrt needed to decide.
+  float d2H, d2Close;
 };
 
 // ---- float4 lane-wise helpers (OpenCL vector semantics, one IEEE op per lane) ----

@@ -193,6 +193,14 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #ifndef LP_OVF
 #define LP_OVF 72
 #endif
+// VAR 2 keeps one 32-bit ENTRY per non-empty group of 16 candidates instead of one 16-bit code per hit:
+// (code of the group's first candidate) << 16 | 16-bit hit mask. ~25 entries per particle on the lattice fluid.
+#ifndef LP_ECAP
+#define LP_ECAP 36
+#endif
+#ifndef LP_EOVF
+#define LP_EOVF 28
+#endif
 
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
 // 256-bit loads of a sweep pass share one address computation.
@@ -243,7 +251,8 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
                                                                     const unsigned *__restrict__ cellStart,
                                                                     int *__restrict__ nb, float *__restrict__ rho,
                                                                     float4 *__restrict__ recA) {
-  __shared__ unsigned short hits[LP_CAP + 1][LP_THREADS];
+  __shared__ unsigned short hits[VAR == 2 ? 1 : LP_CAP + 1][LP_THREADS];
+  __shared__ unsigned ent[VAR == 2 ? LP_ECAP + 1 : 1][LP_THREADS];
   __shared__ int binCount[64], binBase[64];
   __shared__ int binTot0;
   __shared__ unsigned char srcOf[LP_THREADS];
@@ -302,8 +311,9 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr (j == 30)
   const float rfilt2 = rmaxf * rmaxf * 1.0001f;
   const float2 npx = make_float2(-pos.x, -pos.x), npy = make_float2(-pos.y, -pos.y), npz = make_float2(-pos.z, -pos.z);
-  unsigned short ovf[LP_OVF];
-  int n = 0;
+  unsigned short ovf[VAR == 2 ? 1 : LP_OVF];
+  unsigned ovfE[VAR == 2 ? LP_EOVF : 1];
+  int n = 0, ne = 0;
   if (fits && VAR == 2) {
     // half-precision variant: 16 candidates per pass from the cell-local fp16 copy (three 256-bit loads = half the
     // bytes per candidate through the L1 data pipe, which bounds the fp32 sweep). The home particle is expressed in
@@ -341,17 +351,18 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
         };
         lane2(xa.x, ya.x, za.x, 0); lane2(xa.y, ya.y, za.y, 1); lane2(xa.z, ya.z, za.z, 2); lane2(xa.w, ya.w, za.w, 3);
         lane2(xb.x, yb.x, zb.x, 4); lane2(xb.y, yb.y, zb.y, 5); lane2(xb.z, yb.z, zb.z, 6); lane2(xb.w, yb.w, zb.w, 7);
-        // the group is aligned to 16: its ends may reach into the neighbouring cells
-        const unsigned vm = (0xffffu << max(b - j, 0)) & (0xffffu >> max(j + 16 - e, 0));
-        m &= (vm & 0xffu) | ((vm & 0xff00u) << 8);
-        const int v0 = enc + j;
-        while (m) {
-          const int i = __ffs(m);  // 1-based bit; bits 17..24 are candidates 9..16 (1-based)
-          m &= m - 1u;
-          const unsigned short hv = (unsigned short)(v0 + i - ((i > 16) ? 8 : 0));
-          hits[min(nh, LP_CAP)][tid] = hv;  // row LP_CAP is never read
-          if (nh >= LP_CAP) ovf[min(nh - LP_CAP, LP_OVF - 1)] = hv;
-          nh++;
+        // fold to 16 ascending bits; the group is aligned to 16: its ends may reach into the neighbouring cells
+        m = (m & 0xffu) | ((m >> 8) & 0xff00u);
+        m &= (0xffffu << max(b - j, 0)) & (0xffffu >> max(j + 16 - e, 0));
+        // One entry per non-empty group; the hits are unpacked by the select phase, whose loop runs at nearly full
+        // lane occupancy. (Appending hit by hit here cost 27 % of the kernel's instructions at 6 active lanes of 32:
+        // most lanes of a warp have no hit in a given group.)
+        if (m) {
+          const unsigned entry = ((unsigned)(enc + j + 1) << 16) | m;  // code of candidate j + i = (entry >> 16) + i (mod 2^16)
+          ent[min(ne, LP_ECAP)][tid] = entry;  // row LP_ECAP is never read
+          if (ne >= LP_ECAP) ovfE[min(ne - LP_ECAP, LP_EOVF - 1)] = entry;
+          ne++;
+          nh += __popc(m);
         }
       }
     }
@@ -432,7 +443,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
       }
     }
   }
-  if (!fits || n > LP_CAP + LP_OVF) {
+  if (!fits || n > LP_CAP + LP_OVF || ne > LP_ECAP + LP_EOVF) {
     find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
     return;
   }
@@ -483,9 +494,28 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     }
     if (dd <= r2open && found < SPH_NB) take(j, dd);
   };
-  const int nList = min(n, LP_CAP);
-  for (int t = 0; t < nList; t++) first_pass(hits[t][tid]);
-  for (int t = LP_CAP; t < n; t++) first_pass(ovf[t - LP_CAP]);
+  // VAR 2: walk the hits of the entry list in scan order — a flat loop over the n hits (one per iteration for every
+  // lane), fetching the next entry whenever the current mask is used up (entries are never empty)
+  unsigned curMask = 0u, curCode = 0u;
+  int curEntry = 0;
+  auto next_hit = [&]() -> unsigned {
+    if (curMask == 0u) {
+      const unsigned e = (curEntry < LP_ECAP) ? ent[curEntry][tid] : ovfE[min(curEntry - LP_ECAP, LP_EOVF - 1)];
+      curEntry++;
+      curMask = e & 0xffffu;
+      curCode = e >> 16;
+    }
+    const int i = __ffs(curMask) - 1;
+    curMask &= curMask - 1u;
+    return (curCode + (unsigned)i) & 0xffffu;
+  };
+  if (VAR == 2) {
+    for (int t = 0; t < n; t++) first_pass(next_hit());
+  } else {
+    const int nList = min(n, LP_CAP);
+    for (int t = 0; t < nList; t++) first_pass(hits[t][tid]);
+    for (int t = LP_CAP; t < n; t++) first_pass(ovf[t - LP_CAP]);
+  }
   int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
   {
     int sum = 0;
@@ -502,8 +532,10 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     const float r2 = r_thr * r_thr;
     found = 0;
     density = 0.0;
+    curMask = 0u;
+    curEntry = 0;
     for (int t = 0; t < n && found < SPH_NB; t++) {
-      const int j = hit_index((t < LP_CAP) ? hits[t][tid] : ovf[t - LP_CAP]);
+      const int j = hit_index(VAR == 2 ? next_hit() : (unsigned)((t < LP_CAP) ? hits[t][tid] : ovf[t - LP_CAP]));
       if (j == id) continue;
       const float dd = dist2(j);
       if (dd <= r2) take(j, dd);
@@ -532,7 +564,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
 //   rho(t)  the terms of the selected neighbours go to shared memory by slot, lane 0 adds them in slot order (fp64).
 // A particle with more than CP_CAP hits or a cell of more than 8191 particles takes find_neighbors_one (lane 0).
 #ifndef SPH_COOP_MAX_N
-#define SPH_COOP_MAX_N (1 << 18)
+#define SPH_COOP_MAX_N (1 << 17)   // measured: config A (61 k) 0.088 -> 0.059 ms, config B (233 k) 0.136 -> 0.179 ms
 #endif
 #define CP_L 8
 #define CP_THREADS 256

@@ -31,6 +31,15 @@ struct SlabState {
   const SlabRec *myMig[2];
   int nSend[2], nRecv[2], recvStart[2];
   int recut;                      // the faces moved since the last classify (sph_slab_set_cut)
+  // ---- peer-memory exchange (sph_slab_link_* / sph_slab_step): see the "links" section below
+  char *mail;                     // this rank's mailbox (device memory; neighbours write into it)
+  char *peer[2];                  // the neighbours' mailboxes as mapped here: [0] = rank-1, [1] = rank+1
+  bool peerIpc[2];                // opened with cudaIpcOpenMemHandle (to be closed)
+  SlabRec *migLocal[2];           // local copies of the outgoing migrants (they stay here as ghosts)
+  unsigned epoch;                 // step counter = value of the delivery flags of this step
+  int xchg;                       // halo exchanges done in the current step
+  int *doneCounter;               // last-block detection of the send kernels
+  bool stepOpen;                  // between sph_slab_step_begin and _end
 };
 
 struct SlabGeom { int z0, z1, hasDown, hasUp, nOwn, migCap, haloCap, slack; };
@@ -150,7 +159,8 @@ int sph_slab_begin(sph_ctx *c, int n_owned, const uint32_t *gid, int z0, int z1,
   SCU(cudaMalloc(&s->posAlt, 32 * cap)); SCU(cudaMalloc(&s->velAlt, 32 * cap));
   SCU(cudaMemset(s->posAlt, 0, 32 * cap)); SCU(cudaMemset(s->velAlt, 0, 32 * cap));
   SCU(cudaMalloc(&c->tmpRankKey, 4 * cap));
-  SCU(cudaMalloc(&s->counters, 32)); SCU(cudaMallocHost(&s->hostCounters, 32));
+  SCU(cudaMalloc(&s->counters, 32)); SCU(cudaMallocHost(&s->hostCounters, 64));
+  memset(s->hostCounters, 0, 64);
   SCU(cudaHostGetDevicePointer((void **)&s->hostCountersDev, s->hostCounters, 0));
   SCU(cudaMalloc(&s->sendList[0], 4 * (size_t)(halo_cap + mig_cap)));
   SCU(cudaMalloc(&s->sendList[1], 4 * (size_t)(halo_cap + mig_cap)));
@@ -317,6 +327,394 @@ void slab_destroy(sph_ctx *c) {
   // (sph_destroy frees c->position / c->velocity, this frees the Alt side).
   cudaFree(s->gid); cudaFree(s->gidAlt); cudaFree(s->posAlt); cudaFree(s->velAlt);
   cudaFree(s->counters); cudaFreeHost(s->hostCounters); cudaFree(s->sendList[0]); cudaFree(s->sendList[1]);
+  for (int q = 0; q < 2; q++) {
+    if (s->peer[q] && s->peerIpc[q]) cudaIpcCloseMemHandle(s->peer[q]);
+    if (s->migLocal[q]) cudaFree(s->migLocal[q]);
+  }
+  if (s->mail) cudaFree(s->mail);
+  if (s->doneCounter) cudaFree(s->doneCounter);
   delete s;
   c->slab = nullptr;
 }
+
+// =====================================================================================================
+// Links: halo exchange through PEER MEMORY (NVLink / NVSwitch P2P), no NCCL call and no host round trip on the
+// data path. Every rank owns a MAILBOX in device memory; its two neighbours map it (CUDA IPC between processes,
+// peer access inside one process) and their kernels store records, halo values and delivery flags straight into
+// it. A consumer kernel spins on the flag of the delivery it needs. One host synchronisation per step remains:
+// the particle counts after migration size the rank's launches.
+//
+// Mailbox = header | per origin side f (0 = written by rank-1, 1 = written by rank+1):
+//           migrant records [migCap] | ghost records [haloCap] | halo values [2 parities][(haloCap+migCap) x 16 B]
+// Deliveries of a step: slot 0 = records + counts, slot 1 + e = halo exchange e (rho | (p,rho*) | { x* | (p,rho*) }).
+// flag[f][slot] = epoch of the last complete delivery; epochs only grow, nothing is ever reset.
+// Buffer reuse is safe without a handshake: a rank writes delivery e + 2 (same parity as e) only after it has
+// received its neighbour's delivery e + 1, which the neighbour sent after consuming delivery e (stream order);
+// the record buffers of step k + 1 are written after the neighbour's first delivery of step k + 1 is awaited,
+// i.e. after the neighbour consumed everything of step k.
+#define SLAB_SLOTS 16
+struct SlabMailHeader {
+  unsigned flag[2][SLAB_SLOTS];
+  int counts[2][2];   // [origin side]{migrants, ghosts} of the current step
+  unsigned pad[28];
+};
+static_assert(sizeof(SlabMailHeader) == 256, "mailbox header");
+
+struct MailLayout { size_t mig[2], ghost[2], halo[2][2], total; };
+static MailLayout mail_layout(int migCap, int haloCap) {
+  MailLayout m;
+  size_t o = sizeof(SlabMailHeader);
+  auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
+  for (int f = 0; f < 2; f++) {
+    m.mig[f] = take(sizeof(SlabRec) * (size_t)migCap);
+    m.ghost[f] = take(sizeof(SlabRec) * (size_t)haloCap);
+    for (int q = 0; q < 2; q++) m.halo[f][q] = take(16 * (size_t)(haloCap + migCap));
+  }
+  m.total = o;
+  return m;
+}
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Wait until *flag has reached `epoch` (wrap-safe). Gives up after 20 s and raises bit 8 of *err: a lost
+// neighbour must not hang the GPU.
+__device__ __forceinline__ void wait_delivery(const volatile unsigned *flag, unsigned epoch, int *err) {
+  const unsigned long long t0 = global_ns();
+  while ((int)(*flag - epoch) < 0) {
+    __nanosleep(200);
+    if (global_ns() - t0 > 20000000000ull) { atomicOr(err, 256); break; }
+  }
+  __threadfence_system();
+}
+
+// classify of the linked step: k_slab_classify writing into the neighbours' mailboxes, then — last block — the
+// counts and the delivery flag of slot 0, and this rank's own counters to pinned host memory.
+struct SlabLinkOut {
+  SlabRec *mig[2], *ghost[2], *migLocal[2];  // [0] = towards rank-1, [1] = towards rank+1
+  SlabMailHeader *hdr[2];
+  unsigned epoch;
+};
+
+__global__ void __launch_bounds__(256) k_slab_classify_linked(DevParams d, SlabGeom s, SlabLinkOut o,
+                                                              const float4 *__restrict__ pos, const float4 *__restrict__ vel,
+                                                              const unsigned *__restrict__ gid, float4 *__restrict__ posN,
+                                                              float4 *__restrict__ velN, unsigned *__restrict__ gidN,
+                                                              int *__restrict__ listD, int *__restrict__ listU,
+                                                              int *counters, volatile int *hostCounters) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < s.nOwn) {
+    const float4 p = pos[i], v = vel[i];
+    const unsigned g = gid[i];
+    const int cz = (int)(p.z * d.cellSizeInv);
+    SlabRec r;
+    r.pos = p; r.vel = v; r.tag = make_float4(__uint_as_float(g), 0.f, 0.f, 0.f);
+    if ((s.hasDown && cz < s.z0 - 1 - s.slack) || (s.hasUp && cz > s.z1 + s.slack)) atomicOr(&counters[5], 1);
+    if (s.hasDown && cz < s.z0) {
+      const int slot = atomicAdd(&counters[0], 1);
+      if (slot < s.migCap) { o.mig[0][slot] = r; o.migLocal[0][slot] = r; } else atomicOr(&counters[5], 2);
+    } else if (s.hasUp && cz >= s.z1) {
+      const int slot = atomicAdd(&counters[2], 1);
+      if (slot < s.migCap) { o.mig[1][slot] = r; o.migLocal[1][slot] = r; } else atomicOr(&counters[5], 2);
+    } else {
+      const int ni = atomicAdd(&counters[4], 1);
+      posN[ni] = p; velN[ni] = v; gidN[ni] = g;
+      if (s.hasDown && cz == s.z0) {
+        const int slot = atomicAdd(&counters[1], 1);
+        if (slot < s.haloCap) { o.ghost[0][slot] = r; listD[slot] = ni; } else atomicOr(&counters[5], 4);
+      }
+      if (s.hasUp && cz == s.z1 - 1) {
+        const int slot = atomicAdd(&counters[3], 1);
+        if (slot < s.haloCap) { o.ghost[1][slot] = r; listU[slot] = ni; } else atomicOr(&counters[5], 4);
+      }
+    }
+  }
+  // last block: everything every block wrote (also into peer memory) is ordered before the flags
+  __shared__ int last;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(&counters[7], 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence_system();
+  if (threadIdx.x < 8) hostCounters[threadIdx.x] = ((volatile int *)counters)[threadIdx.x];
+  if (threadIdx.x < 2 && o.hdr[threadIdx.x]) {
+    const int side = threadIdx.x;            // towards rank-1 (0) or rank+1 (1); it arrives there from the other side
+    const int from = 1 - side;
+    SlabMailHeader *h = o.hdr[side];
+    const int mig = min(((volatile int *)counters)[2 * side], s.migCap), gh = min(((volatile int *)counters)[2 * side + 1], s.haloCap);
+    ((volatile int *)h->counts[from])[0] = mig;
+    ((volatile int *)h->counts[from])[1] = gh;
+    __threadfence_system();
+    ((volatile unsigned *)h->flag[from])[0] = o.epoch;
+  }
+}
+
+// Wait for the neighbours' record deliveries of this step and hand their counts to the host (pinned, [8..11]).
+__global__ void k_slab_wait_records(SlabMailHeader *mine, int hasDown, int hasUp, unsigned epoch, int *counters,
+                                    volatile int *hostCounters) {
+  const int f = threadIdx.x;  // origin side
+  if (f < 2) {
+    const bool has = f == 0 ? hasDown : hasUp;
+    int mig = 0, gh = 0;
+    if (has) {
+      wait_delivery(&mine->flag[f][0], epoch, &counters[5]);
+      mig = ((volatile int *)mine->counts[f])[0];
+      gh = ((volatile int *)mine->counts[f])[1];
+    }
+    hostCounters[8 + 2 * f] = mig;
+    hostCounters[9 + 2 * f] = gh;
+  }
+  __syncwarp();
+  if (threadIdx.x == 0) hostCounters[5] = ((volatile int *)counters)[5];  // error bits incl. a timeout
+  __threadfence_system();
+}
+
+// Halo refresh, sending half: gather `FIELD` of the particles the two neighbours hold as ghosts and store the values
+// into the neighbours' mailboxes; the last block to finish raises both delivery flags.
+struct SlabHaloSend {
+  int n[2];                 // values towards rank-1, rank+1
+  const int *list[2];       // local original indices
+  void *dst[2];             // halo buffer (this exchange's parity) in the neighbour's mailbox
+  volatile unsigned *flag[2];
+  unsigned epoch;
+};
+
+template <int FIELD>
+__global__ void __launch_bounds__(256) k_slab_halo_send(SlabHaloSend a, const unsigned *__restrict__ back,
+                                                        const float *__restrict__ rho, const float4 *__restrict__ recB,
+                                                        const float4 *__restrict__ spPred, int *doneCounter) {
+  const int total = a.n[0] + a.n[1];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int side = i < a.n[0] ? 0 : 1;
+    const int k = side ? i - a.n[0] : i;
+    const unsigned sid = back[a.list[side][k]];
+    if (FIELD == 0) ((float *)a.dst[side])[k] = rho[sid];
+    if (FIELD == 1) { const float4 q = recB[2 * (size_t)sid + 1]; ((float2 *)a.dst[side])[k] = make_float2(q.x, q.y); }
+    if (FIELD == 2) ((float4 *)a.dst[side])[k] = spPred[sid];
+  }
+  __shared__ int last;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(doneCounter, 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence_system();
+  if (threadIdx.x < 2 && a.flag[threadIdx.x]) *a.flag[threadIdx.x] = a.epoch;
+  if (threadIdx.x == 0) *doneCounter = 0;  // ready for the next send (stream-ordered after this kernel)
+}
+
+// Receiving half: wait for the deliveries, scatter the values into the local ghosts.
+struct SlabHaloRecv {
+  int n[2], first[2];             // ghosts received from rank-1, rank+1: counts and first local original index
+  const void *src[2];             // halo buffer (this exchange's parity) in this rank's mailbox
+  const volatile unsigned *flag[2];
+  unsigned epoch;
+};
+
+template <int FIELD>
+__global__ void __launch_bounds__(256) k_slab_halo_recv(SlabHaloRecv a, const unsigned *__restrict__ back,
+                                                        float *__restrict__ rho, float4 *__restrict__ recA,
+                                                        float4 *__restrict__ recB, float4 *__restrict__ spPred,
+                                                        int *counters) {
+  if (threadIdx.x < 2 && a.flag[threadIdx.x]) wait_delivery(a.flag[threadIdx.x], a.epoch, &counters[5]);
+  __syncthreads();
+  const int total = a.n[0] + a.n[1];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int side = i < a.n[0] ? 0 : 1;
+    const int k = side ? i - a.n[0] : i;
+    const unsigned sid = back[a.first[side] + k];
+    if (FIELD == 0) {
+      const float v = __ldcg((const float *)a.src[side] + k);
+      rho[sid] = v;
+      reinterpret_cast<float *>(recA)[8 * (size_t)sid + 7] = v;
+    }
+    if (FIELD == 1) {
+      const float2 v = __ldcg((const float2 *)a.src[side] + k);
+      recB[2 * (size_t)sid + 1] = make_float4(v.x, v.y, 0.f, 0.f);
+    }
+    if (FIELD == 2) spPred[sid] = __ldcg((const float4 *)a.src[side] + k);
+  }
+}
+
+extern "C" {
+
+int sph_slab_link_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
+
+static int link_alloc(sph_ctx *c) {
+  SlabState *s = c->slab;
+  if (s->mail) return 0;
+  const MailLayout m = mail_layout(s->migCap, s->haloCap);
+  SCU(cudaSetDevice(c->device));
+  SCU(cudaMalloc((void **)&s->mail, m.total));
+  SCU(cudaMemset(s->mail, 0, m.total));
+  for (int q = 0; q < 2; q++) SCU(cudaMalloc((void **)&s->migLocal[q], sizeof(SlabRec) * (size_t)s->migCap));
+  SCU(cudaMalloc((void **)&s->doneCounter, sizeof(int)));
+  SCU(cudaMemset(s->doneCounter, 0, sizeof(int)));
+  return 0;
+}
+
+// Create this rank's mailbox and return its CUDA IPC handle (sph_slab_link_handle_bytes() bytes) for the
+// neighbours in OTHER processes. handle may be NULL when all ranks live in this process.
+int sph_slab_link_export(sph_ctx *c, void *handle) {
+  if (!c || !c->slab) return slab_fail("not a slab context");
+  int rc = link_alloc(c);
+  if (rc) return rc;
+  if (handle) SCU(cudaIpcGetMemHandle((cudaIpcMemHandle_t *)handle, c->slab->mail));
+  return 0;
+}
+
+// Map the mailbox of the neighbour on `side` (0 = rank-1, 1 = rank+1) exported by another process.
+int sph_slab_link_open(sph_ctx *c, int side, const void *handle) {
+  if (!c || !c->slab || side < 0 || side > 1 || !handle) return slab_fail("sph_slab_link_open: bad arguments");
+  SlabState *s = c->slab;
+  SCU(cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof h);
+  void *p = nullptr;
+  SCU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  s->peer[side] = (char *)p;
+  s->peerIpc[side] = true;
+  return 0;
+}
+
+// The neighbour on `side` lives in this process: use its mailbox directly (peer access between the two devices).
+int sph_slab_link_local(sph_ctx *c, int side, sph_ctx *peer) {
+  if (!c || !c->slab || !peer || !peer->slab || side < 0 || side > 1) return slab_fail("sph_slab_link_local: bad arguments");
+  int rc = link_alloc(peer);
+  if (rc) return rc;
+  if (peer->device != c->device) {
+    int can = 0;
+    SCU(cudaDeviceCanAccessPeer(&can, c->device, peer->device));
+    if (!can) return slab_fail("sph_slab_link_local: no peer access between the two devices");
+    SCU(cudaSetDevice(c->device));
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer->device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { slab_fail(cudaGetErrorString(e)); return SPH_E_DEVICE; }
+    cudaGetLastError();
+  }
+  c->slab->peer[side] = peer->slab->mail;
+  c->slab->peerIpc[side] = false;
+  return 0;
+}
+
+// First half of a linked step: classify, deliver migrants + ghost layers to the neighbours, wait for theirs.
+// Asynchronous; every rank of a process must have begun before any of them ends (the end waits for the neighbours).
+int sph_slab_step_begin(sph_ctx *c) {
+  if (!c || !c->slab) return slab_fail("not a slab context");
+  SlabState *s = c->slab;
+  if (!s->mail || (s->hasDown && !s->peer[0]) || (s->hasUp && !s->peer[1])) return slab_fail("sph_slab_step: links are not set up");
+  if (s->stepOpen) return slab_fail("sph_slab_step_begin: the previous step was not ended");
+  SCU(cudaSetDevice(c->device));
+  const MailLayout m = mail_layout(s->migCap, s->haloCap);
+  s->epoch++;
+  s->xchg = 0;
+  SCU(cudaMemsetAsync(s->counters, 0, 32, c->stream));
+  if (c->readPending && c->readSrc == (const void *)s->posAlt) read_fence(c);
+  SlabGeom g = {s->z0, s->z1, s->hasDown, s->hasUp, s->nOwn, s->migCap, s->haloCap, s->recut};
+  s->recut = 0;
+  SlabLinkOut o;
+  for (int side = 0; side < 2; side++) {
+    const bool has = side == 0 ? s->hasDown : s->hasUp;
+    const int from = 1 - side;  // what goes to rank-1 arrives there "from above" and vice versa
+    o.mig[side] = has ? (SlabRec *)(s->peer[side] + m.mig[from]) : nullptr;
+    o.ghost[side] = has ? (SlabRec *)(s->peer[side] + m.ghost[from]) : nullptr;
+    o.hdr[side] = has ? (SlabMailHeader *)s->peer[side] : nullptr;
+    o.migLocal[side] = s->migLocal[side];
+  }
+  o.epoch = s->epoch;
+  k_slab_classify_linked<<<nblk(s->nOwn), 256, 0, c->stream>>>(c->d, g, o, c->position, c->velocity, s->gid, s->posAlt,
+                                                               s->velAlt, s->gidAlt, s->sendList[0], s->sendList[1],
+                                                               s->counters, s->hostCountersDev);
+  k_slab_wait_records<<<1, 32, 0, c->stream>>>((SlabMailHeader *)s->mail, s->hasDown, s->hasUp, s->epoch, s->counters,
+                                               s->hostCountersDev);
+  SCU(cudaGetLastError());
+  s->stepOpen = true;
+  return 0;
+}
+
+static int linked_halo(sph_ctx *c, int field) {
+  SlabState *s = c->slab;
+  const MailLayout m = mail_layout(s->migCap, s->haloCap);
+  const int e = s->xchg++;
+  if (1 + e >= SLAB_SLOTS) return slab_fail("sph_slab_step: too many halo exchanges per step (max_iteration too large)");
+  const int par = e & 1;
+  SlabHaloSend a;
+  SlabHaloRecv b;
+  for (int side = 0; side < 2; side++) {
+    const bool has = side == 0 ? s->hasDown : s->hasUp;
+    const int from = 1 - side;
+    a.n[side] = has ? s->nSend[side] : 0;
+    a.list[side] = s->sendList[side];
+    a.dst[side] = has ? (void *)(s->peer[side] + m.halo[from][par]) : nullptr;
+    a.flag[side] = has ? &((SlabMailHeader *)s->peer[side])->flag[from][1 + e] : nullptr;
+    b.n[side] = has ? s->nRecv[side] : 0;
+    b.first[side] = s->recvStart[side];
+    b.src[side] = s->mail + m.halo[side][par];
+    b.flag[side] = has ? &((SlabMailHeader *)s->mail)->flag[side][1 + e] : nullptr;
+  }
+  a.epoch = b.epoch = s->epoch;
+  float4 *pred = c->sortedPosition + c->d.N;
+  const int gs = min(nblk(a.n[0] + a.n[1]), 4 * c->numSMs), gr = min(nblk(b.n[0] + b.n[1]), 4 * c->numSMs);
+#define SEND(F) k_slab_halo_send<F><<<gs, 256, 0, c->stream>>>(a, c->particleIndexBack, c->rho, c->recB, pred, s->doneCounter)
+#define RECV(F) k_slab_halo_recv<F><<<gr, 256, 0, c->stream>>>(b, c->particleIndexBack, c->rho, c->recA, c->recB, pred, s->counters)
+  if (field == 0) { SEND(0); RECV(0); } else if (field == 1) { SEND(1); RECV(1); } else { SEND(2); RECV(2); }
+#undef SEND
+#undef RECV
+  c->launches += 2;
+  return 0;
+}
+
+int sph_step_part(sph_ctx *c, int part);
+
+// Second half: the one host synchronisation of the step (the counts size the launches), then absorb, and the five
+// parts of the fused step with the halo refreshes between them, all asynchronous.
+int sph_slab_step_end(sph_ctx *c) {
+  if (!c || !c->slab) return slab_fail("not a slab context");
+  SlabState *s = c->slab;
+  if (!s->stepOpen) return slab_fail("sph_slab_step_end without sph_slab_step_begin");
+  s->stepOpen = false;
+  SCU(cudaSetDevice(c->device));
+  SCU(cudaStreamSynchronize(c->stream));
+  const int *h = s->hostCounters;
+  if (h[5] & 256) return slab_fail("timed out waiting for a neighbour's delivery");
+  if (h[5]) return slab_fail(h[5] & 1 ? "a particle crossed more than one cell layer in one step"
+                                       : "migration / halo buffer capacity exceeded");
+  const MailLayout m = mail_layout(s->migCap, s->haloCap);
+  s->migOut[0] = h[0]; s->ghostOut[0] = h[1]; s->migOut[1] = h[2]; s->ghostOut[1] = h[3];
+  s->myMig[0] = s->migLocal[0]; s->myMig[1] = s->migLocal[1];
+  const int incoming[4] = {h[8], h[9], h[10], h[11]};
+  int rc = sph_slab_absorb(c, s->mail + m.mig[0], s->mail + m.ghost[0], s->mail + m.mig[1], s->mail + m.ghost[1], incoming);
+  if (rc) return rc;
+  c->launches += 5;
+  const int iters = c->p.max_iteration < 1 ? 1 : c->p.max_iteration;
+  if ((rc = sph_step_part(c, 0))) return rc;
+  if ((rc = linked_halo(c, 0))) return rc;
+  if ((rc = sph_step_part(c, 1))) return rc;
+  if ((rc = linked_halo(c, 1))) return rc;
+  for (int it = 1; it < iters; it++) {
+    if ((rc = sph_step_part(c, 2))) return rc;
+    if ((rc = linked_halo(c, 2))) return rc;
+    if ((rc = sph_step_part(c, 3))) return rc;
+    if ((rc = linked_halo(c, 1))) return rc;
+  }
+  return sph_step_part(c, 4);
+}
+
+// {migrants down, ghosts down, migrants up, ghosts up} this rank sent in its last step.
+int sph_slab_counts(const sph_ctx *c, int out[4]) {
+  if (!c || !c->slab) return slab_fail("not a slab context");
+  const SlabState *s = c->slab;
+  out[0] = s->migOut[0]; out[1] = s->ghostOut[0]; out[2] = s->migOut[1]; out[3] = s->ghostOut[1];
+  return 0;
+}
+
+// One linked step of a rank that has its process to itself (one process per GPU).
+int sph_slab_step(sph_ctx *c) {
+  int rc = sph_slab_step_begin(c);
+  return rc ? rc : sph_slab_step_end(c);
+}
+
+}  // extern "C"

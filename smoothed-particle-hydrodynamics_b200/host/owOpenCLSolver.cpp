@@ -48,7 +48,7 @@ void owCurrentParams(sph_params *p) {
 owOpenCLSolver::owOpenCLSolver(const float *position_cpp, const float *velocity_cpp,
                                const float *elasticConnectionsData_cpp, const int *membraneData_cpp,
                                const int *particleMembranesList_cpp)
-    : ctx(0) {
+    : ctx(0), fromSnapshot(false) {
   try {
     sph_params p;
     owCurrentParams(&p);
@@ -62,6 +62,8 @@ owOpenCLSolver::owOpenCLSolver(const float *position_cpp, const float *velocity_
     exit(-1);
   }
 }
+
+owOpenCLSolver::owOpenCLSolver(void) : ctx(0), fromSnapshot(false) {}
 
 owOpenCLSolver::~owOpenCLSolver(void) {
   if (ctx) sph_destroy(ctx);
@@ -102,11 +104,20 @@ void owOpenCLSolver::read_position_buffer(float *dst) {
   must(sph_read(ctx, SPH_BUF_POSITION, dst, sizeof(float) * 4 * (size_t)PARTICLE_COUNT), "Could not enqueue read");
 }
 void owOpenCLSolver::read_velocity_buffer(float *dst) {
-  must(sph_read(ctx, SPH_BUF_VELOCITY, dst, sizeof(float) * 4 * (size_t)PARTICLE_COUNT), "Could not enqueue read");
+  const size_t n = sizeof(float) * 4 * (size_t)PARTICLE_COUNT;
+  must(fromSnapshot ? sph_read_snapshot(ctx, SPH_BUF_VELOCITY, dst, n) : sph_read(ctx, SPH_BUF_VELOCITY, dst, n), "Could not enqueue read");
 }
 void owOpenCLSolver::read_density_buffer(float *dst) {
-  must(sph_read(ctx, SPH_BUF_RHO, dst, sizeof(float) * (size_t)PARTICLE_COUNT), "Could not enqueue read");
+  const size_t n = sizeof(float) * (size_t)PARTICLE_COUNT;
+  must(fromSnapshot ? sph_read_snapshot(ctx, SPH_BUF_RHO, dst, n) : sph_read(ctx, SPH_BUF_RHO, dst, n), "Could not enqueue read");
 }
 void owOpenCLSolver::read_particleIndex_buffer(unsigned int *dst) {
-  must(sph_read(ctx, SPH_BUF_PARTICLE_INDEX, dst, sizeof(unsigned int) * 2 * (size_t)PARTICLE_COUNT), "Could not enqueue read");
+  const size_t n = sizeof(unsigned int) * 2 * (size_t)PARTICLE_COUNT;
+  must(fromSnapshot ? sph_read_snapshot(ctx, SPH_BUF_PARTICLE_INDEX, dst, n) : sph_read(ctx, SPH_BUF_PARTICLE_INDEX, dst, n),
+       "Could not enqueue read");
 }
+void owOpenCLSolver::read_position_begin(float *dst) {
+  must(sph_read_begin(ctx, SPH_BUF_POSITION, dst, sizeof(float) * 4 * (size_t)PARTICLE_COUNT), "Could not enqueue read");
+}
+void owOpenCLSolver::read_position_end() { must(sph_read_end(ctx), "Could not finish read"); }
+void owOpenCLSolver::snapshot(bool with_velocity) { must(sph_snapshot(ctx, with_velocity ? 1 : 0), "Could not snapshot"); }

@@ -34,7 +34,7 @@ void owPhysicsFluidSimulator::finishConstruction() {
 
 owPhysicsFluidSimulator::owPhysicsFluidSimulator(owHelper *helper_)
     : ocl_solver(0), position_cpp(0), velocity_cpp(0), elasticConnectionsData_cpp(0), membraneData_cpp(0),
-      particleMembranesList_cpp(0), density_cpp(0), particleIndex_cpp(0), helper(helper_), fused(true), muscleHook(true) {
+      particleMembranesList_cpp(0), density_cpp(0), particleIndex_cpp(0), helper(helper_), fused(true), muscleHook(true), runAhead(true), stepInFlight(false), keepVelocity(false) {
   try {
     numOfLiquidP = numOfElasticP = numOfBoundaryP = numOfElasticConnections = numOfMembranes = 0;
     owHelper::preLoadConfiguration();  // LOAD FROM FILE branch, owPhysicsFluidSimulator.cpp:36-37
@@ -59,7 +59,7 @@ owPhysicsFluidSimulator::owPhysicsFluidSimulator(owHelper *helper_, int particle
                                                  const float *velocity, int numElastic, const float *elastic,
                                                  int numMembranes, const int *membranes, const int *pml)
     : ocl_solver(0), position_cpp(0), velocity_cpp(0), elasticConnectionsData_cpp(0), membraneData_cpp(0),
-      particleMembranesList_cpp(0), density_cpp(0), particleIndex_cpp(0), helper(helper_), fused(true), muscleHook(true) {
+      particleMembranesList_cpp(0), density_cpp(0), particleIndex_cpp(0), helper(helper_), fused(true), muscleHook(true), runAhead(true), stepInFlight(false), keepVelocity(false) {
   try {
     if (particleCount <= 0 || !position || !velocity) throw std::runtime_error("empty scene");
     PARTICLE_COUNT = particleCount;
@@ -100,15 +100,61 @@ owPhysicsFluidSimulator::owPhysicsFluidSimulator(owHelper *helper_, int particle
   }
 }
 
+// :120-130: the step-time banner and the -l_to dump (step 0 with connections and membranes, then every 10th step)
+void owPhysicsFluidSimulator::finishStepOutput(bool load_to) {
+  if (!owHelper::quiet) {
+    printf("------------------------------------\n");
+    printf("_Total_step_time:\t%9.3f ms\n", helper->get_elapsedTime());
+    printf("------------------------------------\n");
+  }
+  if (load_to) {
+    if (iterationCount == 0) owHelper::loadConfigurationToFile(position_cpp, elasticConnectionsData_cpp, membraneData_cpp);
+    else if (iterationCount % iter_step == 0) owHelper::loadConfigurationToFile(position_cpp, NULL, NULL, false);
+  }
+}
+
+// :131-139: ask the Python hook for the next muscle signal and upload it
+void owPhysicsFluidSimulator::nextMuscleSignal() {
+  if (muscleHook && simulation.available()) {
+    std::vector<float> muscle_vector = simulation.run();  // 96 values; signals 96..99 stay 0
+    for (size_t index = 0; index < muscle_vector.size() && (int)index < MUSCLE_COUNT; index++)
+      muscle_activation_signal_cpp[index] = muscle_vector[index];
+  }
+  ocl_solver->updateMuscleActivityData(muscle_activation_signal_cpp);
+}
+
+owPhysicsFluidSimulator::owPhysicsFluidSimulator(void)
+    : ocl_solver(0), position_cpp(0), velocity_cpp(0), elasticConnectionsData_cpp(0), membraneData_cpp(0),
+      particleMembranesList_cpp(0), density_cpp(0), particleIndex_cpp(0), helper(0), fused(true), muscleHook(true),
+      runAhead(true), stepInFlight(false), keepVelocity(false) {}
+
 double owPhysicsFluidSimulator::simulationStep(const bool load_to) {
   int iter = 0;
   helper->refreshTime();
   if (!owHelper::quiet) printf("\n[[ Step %d ]]\n", iterationCount);
   try {
-    if (fused) {
-      // same results as the 18 stages below, as one asynchronous launch sequence; the blocking
-      // position read-back is the synchronisation point
-      if (ocl_solver->_runFusedStep()) throw std::runtime_error(sph_last_error());
+    if (fused || stepInFlight) {
+      // same results as the 18 stages below, as one asynchronous launch sequence
+      if (!stepInFlight && ocl_solver->_runFusedStep()) throw std::runtime_error(sph_last_error());
+      stepInFlight = false;
+      if (fused && runAhead) {
+        // Run ahead: step k is queued (or running). Freeze what the getters of step k read, start the position
+        // read-back on the copy stream, produce the inputs of step k+1 — the muscle signal, which the reference
+        // also updates at the end of the step, before the next one starts (:131-139) — and queue step k+1, whose
+        // integration kernel waits for the read-back. Then block until the positions of step k are in position_cpp.
+        ocl_solver->snapshot(keepVelocity);
+        ocl_solver->setReadFromSnapshot(true);
+        ocl_solver->read_position_begin(position_cpp);
+        nextMuscleSignal();
+        if (ocl_solver->_runFusedStep()) throw std::runtime_error(sph_last_error());
+        stepInFlight = true;
+        ocl_solver->read_position_end();
+        helper->watch_report("_runFusedStep+readBuffer: \t%9.3f ms\n");
+        finishStepOutput(load_to);
+        iterationCount++;
+        return helper->get_elapsedTime();
+      }
+      ocl_solver->setReadFromSnapshot(false);
       ocl_solver->read_position_buffer(position_cpp);
       helper->watch_report("_runFusedStep+readBuffer: \t%9.3f ms\n");
     } else {
@@ -137,22 +183,9 @@ double owPhysicsFluidSimulator::simulationStep(const bool load_to) {
       ocl_solver->read_position_buffer(position_cpp);
       helper->watch_report("_readBuffer: \t\t%9.3f ms\n");
     }
-    if (!owHelper::quiet) {
-      printf("------------------------------------\n");
-      printf("_Total_step_time:\t%9.3f ms\n", helper->get_elapsedTime());
-      printf("------------------------------------\n");
-    }
-    if (load_to) {
-      if (iterationCount == 0) owHelper::loadConfigurationToFile(position_cpp, elasticConnectionsData_cpp, membraneData_cpp);
-      else if (iterationCount % iter_step == 0) owHelper::loadConfigurationToFile(position_cpp, NULL, NULL, false);
-    }
+    finishStepOutput(load_to);
     iterationCount++;
-    if (muscleHook && simulation.available()) {
-      std::vector<float> muscle_vector = simulation.run();  // 96 values; signals 96..99 stay 0 (§8a.2 item 10)
-      for (size_t index = 0; index < muscle_vector.size() && (int)index < MUSCLE_COUNT; index++)
-        muscle_activation_signal_cpp[index] = muscle_vector[index];
-    }
-    ocl_solver->updateMuscleActivityData(muscle_activation_signal_cpp);
+    nextMuscleSignal();
     return helper->get_elapsedTime();
   } catch (std::exception &e) {
     std::cout << "ERROR: " << e.what() << std::endl;

@@ -19,6 +19,7 @@ ow_sim *ow_sim_create_from_files(void) {
   ow_sim *s = new ow_sim;
   s->helper = new owHelper();
   s->sim = new owPhysicsFluidSimulator(s->helper);
+  s->sim->setKeepVelocity(true);  // the tests read velocities back
   return s;
 }
 ow_sim *ow_sim_create(int n, const float *pos, const float *vel, int ne, const float *elastic, int nm,
@@ -26,11 +27,14 @@ ow_sim *ow_sim_create(int n, const float *pos, const float *vel, int ne, const f
   ow_sim *s = new ow_sim;
   s->helper = new owHelper();
   s->sim = new owPhysicsFluidSimulator(s->helper, n, pos, vel, ne, elastic, nm, membranes, pml);
+  s->sim->setKeepVelocity(true);  // the tests read velocities back
   return s;
 }
 void ow_sim_destroy(ow_sim *s) { if (s) { delete s->sim; delete s->helper; delete s; } }
 double ow_sim_step(ow_sim *s, int load_to) { return s->sim->simulationStep(load_to != 0); }
 void ow_sim_set_fused(ow_sim *s, int on) { s->sim->setFused(on != 0); }
+void ow_sim_set_run_ahead(ow_sim *s, int on) { s->sim->setRunAhead(on != 0); }
+void ow_sim_set_keep_velocity(ow_sim *s, int on) { s->sim->setKeepVelocity(on != 0); }
 void ow_sim_set_muscle_hook(ow_sim *s, int on) { s->sim->setMuscleHook(on != 0); }
 void ow_sim_set_muscle_callback(ow_sim *s, ow_muscle_callback cb, void *user) { s->sim->muscleSimulation().setCallback(cb, user); }
 const float *ow_sim_position(ow_sim *s) { return s->sim->getPosition_cpp(); }

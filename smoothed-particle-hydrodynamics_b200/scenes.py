@@ -129,17 +129,20 @@ def boundary_box_slab(bx, by, bz, k0, k1):
     return pos, vel, ids
 
 
-def slab_scene(name, world, rank, seed=12345, jitter_frac=0.05, margin=3):
-    """Weak-scaling scene: the named fluid stacked `world` times along z in one box,
-    cut into `world` slabs of whole hash-cell layers; returns what ONE rank needs:
-    dict(position, velocity, gid, z0, z1, box, n_total, halo_cap, mig_cap). Only this rank's part is generated."""
+def slab_scene(name, world, rank, seed=12345, jitter_frac=0.05, margin=3, stack=None):
+    """One rank's part of a slab-decomposed fluid: the named fluid stacked `stack` times along z in one box and cut
+    into `world` slabs of whole hash-cell layers. stack = world (default) is the weak-scaling scene (SURVEY.md §8d
+    config E: every rank owns one copy of the workload), stack = 1 the strong-scaling one (config D: ONE fluid
+    divided among the ranks). Returns dict(position, velocity, gid, z0, z1, box, n_total, halo_cap, mig_cap);
+    only this rank's part is generated."""
     nx, ny, nz, fill = WORKLOADS[name]
-    nzt = nz * world
-    bx, by, bz = nx + 2 * margin, ny + 2 * margin, (nzt if fill is None else fill * world) + 2 * margin
+    stack = world if stack is None else int(stack)
+    nzt = nz * stack
+    bx, by, bz = nx + 2 * margin, ny + 2 * margin, (nzt if fill is None else fill * stack) + 2 * margin
     bx, by, bz = bx + (bx & 1), by + (by & 1), bz + (bz & 1)
     gz = int(bz / 2.0) + 1  # (int)((zmax - zmin) / h) + 1 with zmax = (bz/2) * h, owOpenCLSolver.cpp:14-17
     cell_inv = np.float32(1.0) / (np.float32(2.0) * H)
-    cuts = [0] + [(margin + r * nz) // 4 for r in range(1, world)] + [gz]
+    cuts = [0] + [(margin + (r * nzt) // world) // 4 for r in range(1, world)] + [gz]
     z0, z1 = cuts[rank], cuts[rank + 1]
     # lattice / box layers that can fall into cell layers [z0, z1): 4 r0 per cell, one spare layer for the jitter
     lo, hi = 4 * z0 - 1, 4 * z1 + 1

@@ -20,6 +20,7 @@ import numpy as np
 DOWN, UP = 0, 1
 RHO, PRS, XPRED = 0, 1, 2
 FIELD_BYTES = {RHO: 4, PRS: 8, XPRED: 16}
+EXTRA_LAUNCHES_PER_STEP = 4 + 14   # classify / append / iota x 2 + the 7 x 2 pack / unpack kernels (not in sph_launch_count)
 
 
 def cell_layer(z, cell_size_inv):
@@ -104,6 +105,14 @@ class SlabRank:
         L.sph_device_free.argtypes = [V]
         L.sph_device_free.restype = None
         L.sph_device_copy.argtypes = [V, V, C.c_size_t]
+        if hasattr(L, "sph_slab_link_export"):   # peer-memory exchange (CUDA library only)
+            L.sph_slab_link_export.argtypes = [V, V]
+            L.sph_slab_link_open.argtypes = [V, I, V]
+            L.sph_slab_link_local.argtypes = [V, I, V]
+            L.sph_slab_step.argtypes = [V]
+            L.sph_slab_step_begin.argtypes = [V]
+            L.sph_slab_step_end.argtypes = [V]
+            L.sph_slab_counts.argtypes = [V, C.POINTER(I)]
 
     def _check(self, rc, what):
         if rc != 0:
@@ -179,6 +188,36 @@ class SlabRank:
 
     def close(self):
         self.ctx.close()
+
+    # -- links: the neighbours' kernels write into this rank's mailbox (csrc/sph_slab.cu, "Links")
+    def link_export(self):
+        """Create the mailbox; returns its CUDA IPC handle (bytes) for neighbours in other processes."""
+        n = self.lib.sph_slab_link_handle_bytes()
+        buf = (C.c_char * n)()
+        self._check(self.lib.sph_slab_link_export(self.ctx.h, buf), "sph_slab_link_export")
+        return bytes(buf)
+
+    def link_open(self, side, handle):
+        buf = (C.c_char * len(handle)).from_buffer_copy(handle)
+        self._check(self.lib.sph_slab_link_open(self.ctx.h, side, buf), "sph_slab_link_open")
+
+    def link_local(self, side, other):
+        self._check(self.lib.sph_slab_link_local(self.ctx.h, side, other.ctx.h), "sph_slab_link_local")
+
+    def step_linked(self):
+        self.step_begin()
+        self.step_end()
+
+    def step_begin(self):
+        self._check(self.lib.sph_slab_step_begin(self.ctx.h), "sph_slab_step_begin")
+
+    def step_end(self):
+        self._check(self.lib.sph_slab_step_end(self.ctx.h), "sph_slab_step_end")
+        out = (C.c_int * 4)()
+        self._check(self.lib.sph_slab_counts(self.ctx.h, out), "sph_slab_counts")
+        self.counts = list(out)
+        info = self.info()
+        self.n_send, self.n_recv = info[2:4], info[4:6]
 
 
 class RawBuffer:
@@ -304,9 +343,65 @@ class DistTransport:
         self._move("halo_out", "halo_in", [r.n_send[DOWN] * b, r.n_send[UP] * b], [r.n_recv[DOWN] * b, r.n_recv[UP] * b])
 
 
+class PeerTransport:
+    """Exchange through peer memory (NVLink / NVSwitch P2P, or plain device memory when the ranks share a GPU): the
+    whole step, halo refreshes included, runs inside the library (sph_slab_step_begin / _end); nothing travels through
+    Python, NCCL or the host. Two set-ups:
+      PeerTransport.local(ranks)        all ranks in this process (tests on one GPU, a C++-style multi-GPU host);
+      PeerTransport.distributed(rank)   one rank per process: the mailbox handles (CUDA IPC) are exchanged once through
+                                        torch.distributed's object all-gather, then torch is out of the picture."""
+    linked = True
+
+    def __init__(self, ranks):
+        self.ranks = ranks
+
+    @classmethod
+    def local(cls, ranks):
+        for r in ranks:
+            r.link_export()
+        for i, r in enumerate(ranks):
+            if r.has[DOWN]:
+                r.link_local(DOWN, ranks[i - 1])
+            if r.has[UP]:
+                r.link_local(UP, ranks[i + 1])
+        return cls(ranks)
+
+    @classmethod
+    def distributed(cls, rank_obj):
+        import torch.distributed as dist
+        me, world = dist.get_rank(), dist.get_world_size()
+        handles = [None] * world
+        dist.all_gather_object(handles, rank_obj.link_export())
+        if rank_obj.has[DOWN]:
+            rank_obj.link_open(DOWN, handles[me - 1])
+        if rank_obj.has[UP]:
+            rank_obj.link_open(UP, handles[me + 1])
+        dist.barrier()
+        return cls([rank_obj])
+
+    def all_gather(self, rows):
+        if len(self.ranks) > 1:
+            return [list(x) for x in rows]
+        import torch
+        import torch.distributed as dist
+        mine = torch.tensor(rows[0], dtype=torch.int64)
+        out = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+        dist.all_gather(out, mine)
+        return [t.tolist() for t in out]
+
+    def step(self):
+        for r in self.ranks:      # every rank delivers before any rank waits for its neighbours
+            r.step_begin()
+        for r in self.ranks:
+            r.step_end()
+
+
 def slab_step(transport):
     """One PCISPH step of every rank the transport drives (all of them for loopback, this process's for dist)."""
     ranks = transport.ranks
+    if getattr(transport, "linked", False):
+        transport.step()
+        return
 
     def halo(field):
         for r in ranks:

@@ -30,6 +30,23 @@ def P():
     return common.product_lib()
 
 
+@pytest.fixture(scope="module", autouse=True, params=["loopback", "peer"])
+def transport_kind(request):
+    """loopback: the library packs / unpacks, the test copies the bytes between the ranks' buffers (round-1 protocol,
+    what the NCCL transport also drives). peer: the ranks' kernels write into each other's mailboxes and the whole step
+    runs inside the library (sph_slab_step_begin / _end) — the product path of bench.py --gpus N."""
+    global KIND
+    KIND = request.param
+    yield request.param
+
+
+KIND = "loopback"
+
+
+def make_transport(ranks):
+    return slab.PeerTransport.local(ranks) if KIND == "peer" else slab.LoopbackTransport(ranks)
+
+
 def moving_fluid(seed=7):
     """A liquid column in a tall box, thrown along z so that whole layers of particles change slab."""
     pos, vel = common.synthetic_block(14, 12, 40, (24, 22, 96), seed=seed)
@@ -60,7 +77,7 @@ def run_slabs(P, p, pos, vel, world, steps):
     slabs, caps = slab.split_fluid(p, pos, world)
     for r, (z0, z1, own) in enumerate(slabs):
         ranks.append(slab.SlabRank(P, p, pos[own], vel[own], own.astype(np.uint32), z0, z1, r, world, **caps))
-    tr = slab.LoopbackTransport(ranks)
+    tr = make_transport(ranks)
     moved = 0
     for _ in range(steps):
         slab.slab_step(tr)
@@ -124,7 +141,7 @@ def test_slab_recut_hands_layers_over(P):
         own = np.nonzero((cz >= cuts[r]) & (cz < cuts[r + 1]))[0]
         ranks.append(slab.SlabRank(P, p, pos[own], vel[own], own.astype(np.uint32), cuts[r], cuts[r + 1], r, 3,
                                    capacity=len(pos) + 4 * caps["halo_cap"], **caps))
-    tr = slab.LoopbackTransport(ranks)
+    tr = make_transport(ranks)
     moves, sizes = 0, []
     for s in range(steps):
         if s < 6:
