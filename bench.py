@@ -362,12 +362,21 @@ def time_slab(slab, torch, dist, L, r, tr, warmup, steps, e2e=True):
         slab.slab_step(tr)
         r._check(r.lib.sph_slab_read_owned(r.ctx.h, host_pos[0].ctypes.data_as(C.c_void_p), None, None), "read_owned")
 
+    marks = []
+
     def pipelined(s):
+        t = [time.perf_counter()]
         host_sig[s & 1][:] = muscle_signal(s)
         r.ctx.set_muscles(host_sig[s & 1])
-        slab.slab_step(tr)
-        r.ctx.read_end()
-        r.read_owned_begin(host_pos[s & 1])
+        t.append(time.perf_counter())
+        if linked:
+            r.step_begin(); t.append(time.perf_counter())
+            r.step_end(); t.append(time.perf_counter())
+        else:
+            slab.slab_step(tr); t.append(time.perf_counter())
+        r.ctx.read_end(); t.append(time.perf_counter())
+        r.read_owned_begin(host_pos[s & 1]); t.append(time.perf_counter())
+        marks.append([round((b - a) * 1e3, 2) for a, b in zip(t, t[1:])])
 
     blocking(0)
     dist.barrier()
@@ -386,6 +395,8 @@ def time_slab(slab, torch, dist, L, r, tr, warmup, steps, e2e=True):
     r.ctx.read_end()
     out["e2e_ms"] = (time.perf_counter() - t0) * 1e3 / e2e_steps
     out["e2e_steps"] = e2e_steps
+    if os.environ.get("SPH_BENCH_MARKS"):   # host-side timeline of the pipelined loop: muscles | [begin | end] or step | read_end | read_begin
+        print("rank %d marks %s" % (r.index, marks[-4:]), file=sys.stderr, flush=True)
     return out
 
 

@@ -16,6 +16,10 @@
 
 int sph_scan_tiles_for(int n);
 
+// Ask for eager module loading when this library is loaded before CUDA is initialised (see preload() in
+// sph_sort.cu for why lazily loaded kernels and flag-waiting kernels do not mix); harmless otherwise.
+__attribute__((constructor)) static void sph_library_init() { setenv("CUDA_MODULE_LOADING", "EAGER", 0); }
+
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) { g_err = msg; return code; }
 
@@ -183,7 +187,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soa, c->tmpRankKey};
+                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soa, c->tmpRankKey, c->memList, c->memCount};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -306,6 +310,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
     A(dalloc(&c->pml, 7 * (size_t)p->num_elastic));
     if (ok) A(cudaMemcpy(c->pml, pml7, 28 * (size_t)p->num_elastic, cudaMemcpyHostToDevice));
     if (ok) A(dalloc(&c->elasticMask, N));
+    if (ok) A(dalloc(&c->memList, N));
+    if (ok) A(dalloc(&c->memCount, 1));
   }
   if (ok && c->has_elastic) {                                                  // :83-86
     A(dalloc(&c->elastic, (size_t)SPH_NB * p->num_elastic));
@@ -401,16 +407,20 @@ struct ProfScope {
 // Membrane interaction + finalize of the fused step. Without a membrane list the kernel would only zero the
 // displacement half of `position` (clearMembraneBuffers) and add +0 (finalize): the integration kernel has
 // folded the add in, and the displacement half is zeroed once per upload instead of once per step.
+// clearMembraneBuffers zeroes both upper halves every step (sphFluid.cl:1224-1225). Nothing in the fused step writes
+// them except the membrane kernels (which keep them zeroed themselves), so they are cleared once per upload.
+static void clear_upper_halves_if_dirty(sph_ctx *c) {
+  if (!c->dispDirty) return;
+  cudaMemsetAsync(c->position + c->d.N, 0, 16 * (size_t)c->d.N, c->stream);
+  cudaMemsetAsync(c->velocity + c->d.N, 0, 16 * (size_t)c->d.N, c->stream);
+  c->dispDirty = false;
+}
+
 static int fused_membranes(sph_ctx *c) {
   if (c->has_pml) {
     ProfScope s(c, PK_MEMBRANES);
     launch_membrane_interaction(c, true);
     return 2;
-  }
-  if (c->dispDirty) {  // clearMembraneBuffers zeroes both upper halves (sphFluid.cl:1224-1225)
-    cudaMemsetAsync(c->position + c->d.N, 0, 16 * (size_t)c->d.N, c->stream);
-    cudaMemsetAsync(c->velocity + c->d.N, 0, 16 * (size_t)c->d.N, c->stream);
-    c->dispDirty = false;
   }
   return 0;
 }
@@ -463,6 +473,7 @@ static int capture_half(sph_ctx *c, int half) {
 int sph_step(sph_ctx *c) {
   if (!c) return fail(SPH_E_INVALID, "null ctx");
   CU(cudaSetDevice(c->device));
+  clear_upper_halves_if_dirty(c);
   if (!want_graph(c)) {
     c->launches += step_body(c, 0);
     c->launches += step_body(c, 1);
@@ -471,7 +482,6 @@ int sph_step(sph_ctx *c) {
   // Graph replay: small scenes are launch-bound (a dozen dependent kernels of a few microseconds each). What a
   // replay cannot carry sits between the two graphs: the wait for a pipelined read-back, and the once-per-upload
   // clearing of the displacement halves in front.
-  if (!c->has_pml && c->dispDirty) fused_membranes(c);
   if (c->stepGraph[0] && c->graphStream != c->stream) drop_graph(c);
   if (!c->stepGraph[0]) {
     int rc = capture_half(c, 0);
@@ -498,6 +508,7 @@ int sph_step_part(sph_ctx *c, int part) {
   CU(cudaSetDevice(c->device));
   switch (part) {
     case 0:
+      clear_upper_halves_if_dirty(c);
       { ProfScope s(c, PK_HASH); launch_hash_count(c, false); }
       { ProfScope s(c, PK_SORT); launch_sort(c, true); }
       { ProfScope s(c, PK_NEIGHBORS); launch_find_neighbors(c, true); }

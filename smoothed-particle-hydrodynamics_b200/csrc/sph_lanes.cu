@@ -147,7 +147,8 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevPara
                                                                      const uint2 *__restrict__ particleIndex,
                                                                      float4 *__restrict__ position,
                                                                      float4 *__restrict__ velocity,
-                                                                     unsigned *__restrict__ elasticMask) {
+                                                                     unsigned *__restrict__ elasticMask,
+                                                                     int *__restrict__ memList, int *__restrict__ memCount) {
   using G = LaneGeom<L>;
   __shared__ float term[3 * G::CS];
   const int t = threadIdx.x, pl = t / L, l = t % L;
@@ -212,10 +213,12 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevPara
   const float4 result = f4(rx * cf, ry * cf, rz * cf, 0.f);
   acc[d.N + id] = result;
   if (MODE == 1) spPred[id] = predict_position(d, sp[id], sv[id], result);
-  if (MODE == 2 && elasticMask) elasticMask[id] = emask;
-  if (MODE == 2)
-    integrate_particle(d, id, sp[id], sv[id], acc[id] + result, pi.w, particleIndex[id].y, bmask, spT, sv, nb, position,
-                       velocity, /*foldFinalize=*/elasticMask == nullptr);
+  if (MODE == 2) {
+    const unsigned serial = particleIndex[id].y;
+    integrate_particle(d, id, sp[id], sv[id], acc[id] + result, pi.w, serial, bmask, spT, sv, nb, position, velocity,
+                       /*foldFinalize=*/elasticMask == nullptr);
+    if (elasticMask) membrane_prologue(d, id, serial, emask, pi.w, elasticMask, memList, memCount, position, velocity);
+  }
 }
 
 // ---------------------------------------------------------------- launchers
@@ -246,7 +249,7 @@ bool launch_predict_density_lanes(sph_ctx *c, int L) {
 bool launch_pressure_force_lanes(sph_ctx *c, int mode, int L) {
   float4 *pred = c->sortedPosition + c->d.N;
 #define P_ARGS c->d, c->spT, c->sortedVelocity, c->nbIds, c->recB, c->acceleration, c->sortedPosition, pred, c->particleIndex, \
-               c->position, c->velocity, c->elasticMask
+               c->position, c->velocity, c->elasticMask, c->memList, c->memCount
 #define P_LAUNCH(M, LL) k_pressure_force_lanes<M, LL><<<lanes_grid<LL>(c->d.N), LaneGeom<LL>::T, 0, c->stream>>>(P_ARGS)
   if (mode != 1 && mode != 2) return false;
   if (L == 4) { if (mode == 1) P_LAUNCH(1, 4); else P_LAUNCH(2, 4); }
@@ -256,4 +259,22 @@ bool launch_pressure_force_lanes(sph_ctx *c, int mode, int L) {
 #undef P_LAUNCH
 #undef P_ARGS
   return true;
+}
+
+// Force the (lazily loaded, CUDA >= 12.2) code of this file's step kernels onto the device. A kernel that spins on a
+// neighbour's delivery flag (sph_slab.cu) must never be resident while the host loads another kernel for the first
+// time — module loading synchronises the context and would wait for the spinning kernel forever.
+static void preload(const void *const *fns, int n) {
+  cudaFuncAttributes a;
+  for (int i = 0; i < n; i++) cudaFuncGetAttributes(&a, fns[i]);
+  cudaGetLastError();
+}
+void preload_lanes_kernels() {
+  const void *const f[] = {(const void *)k_forces_lanes<4>, (const void *)k_forces_lanes<8>, (const void *)k_forces_lanes<16>,
+                           (const void *)k_predict_density_lanes<4>, (const void *)k_predict_density_lanes<8>,
+                           (const void *)k_predict_density_lanes<16>, (const void *)k_pressure_force_lanes<1, 4>,
+                           (const void *)k_pressure_force_lanes<1, 8>, (const void *)k_pressure_force_lanes<1, 16>,
+                           (const void *)k_pressure_force_lanes<2, 4>, (const void *)k_pressure_force_lanes<2, 8>,
+                           (const void *)k_pressure_force_lanes<2, 16>};
+  preload(f, sizeof f / sizeof f[0]);
 }

@@ -1375,3 +1375,20 @@ void launch_materialize_neighbor_map(sph_ctx *c, float2 *out) {
   size_t n = (size_t)c->d.N * SPH_NB;
   k_materialize_neighbor_map<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->d, c->sortedPosition, c->nbIds, out);
 }
+
+// Force the (lazily loaded, CUDA >= 12.2) code of this file's step kernels onto the device. A kernel that spins on a
+// neighbour's delivery flag (sph_slab.cu) must never be resident while the host loads another kernel for the first
+// time — module loading synchronises the context and would wait for the spinning kernel forever.
+static void preload(const void *const *fns, int n) {
+  cudaFuncAttributes a;
+  for (int i = 0; i < n; i++) cudaFuncGetAttributes(&a, fns[i]);
+  cudaGetLastError();
+}
+void preload_neighbor_kernels() {
+  const void *const f[] = {(const void *)k_soa_positions, (const void *)k_soa_positions_half,
+                           (const void *)k_find_neighbors_list<true, 0>, (const void *)k_find_neighbors_list<true, 1>,
+                           (const void *)k_find_neighbors_list<true, 2>, (const void *)k_find_neighbors_coop<true>,
+                           (const void *)k_find_neighbors_generic<true>, (const void *)k_neighbor_tiles<true>,
+                           (const void *)k_neighbors_deferred<true>};
+  preload(f, sizeof f / sizeof f[0]);
+}

@@ -380,13 +380,13 @@ __device__ __forceinline__ unsigned long long global_ns() {
   return t;
 }
 
-// Wait until *flag has reached `epoch` (wrap-safe). Gives up after 20 s and raises bit 8 of *err: a lost
+// Wait until *flag has reached `epoch` (wrap-safe). Gives up after 10 s and raises the sticky error word *err: a lost
 // neighbour must not hang the GPU.
 __device__ __forceinline__ void wait_delivery(const volatile unsigned *flag, unsigned epoch, int *err) {
   const unsigned long long t0 = global_ns();
   while ((int)(*flag - epoch) < 0) {
     __nanosleep(200);
-    if (global_ns() - t0 > 20000000000ull) { atomicOr(err, 256); break; }
+    if (global_ns() - t0 > 10000000000ull) { atomicOr(err, 256); break; }
   }
   __threadfence_system();
 }
@@ -455,13 +455,13 @@ __global__ void __launch_bounds__(256) k_slab_classify_linked(DevParams d, SlabG
 
 // Wait for the neighbours' record deliveries of this step and hand their counts to the host (pinned, [8..11]).
 __global__ void k_slab_wait_records(SlabMailHeader *mine, int hasDown, int hasUp, unsigned epoch, int *counters,
-                                    volatile int *hostCounters) {
+                                    volatile int *hostCounters, int *sticky) {
   const int f = threadIdx.x;  // origin side
   if (f < 2) {
     const bool has = f == 0 ? hasDown : hasUp;
     int mig = 0, gh = 0;
     if (has) {
-      wait_delivery(&mine->flag[f][0], epoch, &counters[5]);
+      wait_delivery(&mine->flag[f][0], epoch, sticky);
       mig = ((volatile int *)mine->counts[f])[0];
       gh = ((volatile int *)mine->counts[f])[1];
     }
@@ -469,7 +469,10 @@ __global__ void k_slab_wait_records(SlabMailHeader *mine, int hasDown, int hasUp
     hostCounters[9 + 2 * f] = gh;
   }
   __syncwarp();
-  if (threadIdx.x == 0) hostCounters[5] = ((volatile int *)counters)[5];  // error bits incl. a timeout
+  if (threadIdx.x == 0) {
+    hostCounters[5] = ((volatile int *)counters)[5];
+    hostCounters[6] = *(volatile int *)sticky;   // a delivery of this or an earlier step timed out
+  }
   __threadfence_system();
 }
 
@@ -519,8 +522,8 @@ template <int FIELD>
 __global__ void __launch_bounds__(256) k_slab_halo_recv(SlabHaloRecv a, const unsigned *__restrict__ back,
                                                         float *__restrict__ rho, float4 *__restrict__ recA,
                                                         float4 *__restrict__ recB, float4 *__restrict__ spPred,
-                                                        int *counters) {
-  if (threadIdx.x < 2 && a.flag[threadIdx.x]) wait_delivery(a.flag[threadIdx.x], a.epoch, &counters[5]);
+                                                        int *sticky) {
+  if (threadIdx.x < 2 && a.flag[threadIdx.x]) wait_delivery(a.flag[threadIdx.x], a.epoch, sticky);
   __syncthreads();
   const int total = a.n[0] + a.n[1];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -540,6 +543,29 @@ __global__ void __launch_bounds__(256) k_slab_halo_recv(SlabHaloRecv a, const un
   }
 }
 
+void preload_sort_kernels();
+void preload_neighbor_kernels();
+void preload_pcisph_kernels();
+void preload_membrane_kernels();
+
+// see preload() in sph_sort.cu: everything a linked step launches is loaded before the first flag is waited for
+static void preload_step_kernels() {
+  static bool done = false;
+  if (done) return;
+  done = true;
+  preload_sort_kernels();
+  preload_neighbor_kernels();
+  preload_pcisph_kernels();
+  preload_membrane_kernels();
+  const void *const f[] = {(const void *)k_slab_classify_linked, (const void *)k_slab_wait_records, (const void *)k_slab_append,
+                           (const void *)k_slab_iota, (const void *)k_slab_halo_send<0>, (const void *)k_slab_halo_send<1>,
+                           (const void *)k_slab_halo_send<2>, (const void *)k_slab_halo_recv<0>, (const void *)k_slab_halo_recv<1>,
+                           (const void *)k_slab_halo_recv<2>};
+  cudaFuncAttributes a;
+  for (const void *k : f) cudaFuncGetAttributes(&a, k);
+  cudaGetLastError();
+}
+
 extern "C" {
 
 int sph_slab_link_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
@@ -547,13 +573,14 @@ int sph_slab_link_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
 static int link_alloc(sph_ctx *c) {
   SlabState *s = c->slab;
   if (s->mail) return 0;
+  preload_step_kernels();
   const MailLayout m = mail_layout(s->migCap, s->haloCap);
   SCU(cudaSetDevice(c->device));
   SCU(cudaMalloc((void **)&s->mail, m.total));
   SCU(cudaMemset(s->mail, 0, m.total));
   for (int q = 0; q < 2; q++) SCU(cudaMalloc((void **)&s->migLocal[q], sizeof(SlabRec) * (size_t)s->migCap));
-  SCU(cudaMalloc((void **)&s->doneCounter, sizeof(int)));
-  SCU(cudaMemset(s->doneCounter, 0, sizeof(int)));
+  SCU(cudaMalloc((void **)&s->doneCounter, 2 * sizeof(int)));   // [0] last-block counter, [1] sticky error word (delivery timeouts)
+  SCU(cudaMemset(s->doneCounter, 0, 2 * sizeof(int)));
   return 0;
 }
 
@@ -629,7 +656,7 @@ int sph_slab_step_begin(sph_ctx *c) {
                                                                s->velAlt, s->gidAlt, s->sendList[0], s->sendList[1],
                                                                s->counters, s->hostCountersDev);
   k_slab_wait_records<<<1, 32, 0, c->stream>>>((SlabMailHeader *)s->mail, s->hasDown, s->hasUp, s->epoch, s->counters,
-                                               s->hostCountersDev);
+                                               s->hostCountersDev, s->doneCounter + 1);
   SCU(cudaGetLastError());
   s->stepOpen = true;
   return 0;
@@ -659,7 +686,7 @@ static int linked_halo(sph_ctx *c, int field) {
   float4 *pred = c->sortedPosition + c->d.N;
   const int gs = min(nblk(a.n[0] + a.n[1]), 4 * c->numSMs), gr = min(nblk(b.n[0] + b.n[1]), 4 * c->numSMs);
 #define SEND(F) k_slab_halo_send<F><<<gs, 256, 0, c->stream>>>(a, c->particleIndexBack, c->rho, c->recB, pred, s->doneCounter)
-#define RECV(F) k_slab_halo_recv<F><<<gr, 256, 0, c->stream>>>(b, c->particleIndexBack, c->rho, c->recA, c->recB, pred, s->counters)
+#define RECV(F) k_slab_halo_recv<F><<<gr, 256, 0, c->stream>>>(b, c->particleIndexBack, c->rho, c->recA, c->recB, pred, s->doneCounter + 1)
   if (field == 0) { SEND(0); RECV(0); } else if (field == 1) { SEND(1); RECV(1); } else { SEND(2); RECV(2); }
 #undef SEND
 #undef RECV
@@ -679,7 +706,7 @@ int sph_slab_step_end(sph_ctx *c) {
   SCU(cudaSetDevice(c->device));
   SCU(cudaStreamSynchronize(c->stream));
   const int *h = s->hostCounters;
-  if (h[5] & 256) return slab_fail("timed out waiting for a neighbour's delivery");
+  if (h[6]) return slab_fail("timed out waiting for a neighbour's delivery (the neighbour failed, or never stepped)");
   if (h[5]) return slab_fail(h[5] & 1 ? "a particle crossed more than one cell layer in one step"
                                        : "migration / halo buffer capacity exceeded");
   const MailLayout m = mail_layout(s->migCap, s->haloCap);

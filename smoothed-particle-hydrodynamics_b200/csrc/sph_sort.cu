@@ -264,3 +264,17 @@ void launch_indexx_compat(sph_ctx *c) {
 }
 
 int sph_scan_tiles_for(int n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
+
+// Force the (lazily loaded, CUDA >= 12.2) code of this file's step kernels onto the device. A kernel that spins on a
+// neighbour's delivery flag (sph_slab.cu) must never be resident while the host loads another kernel for the first
+// time — module loading synchronises the context and would wait for the spinning kernel forever.
+static void preload(const void *const *fns, int n) {
+  cudaFuncAttributes a;
+  for (int i = 0; i < n; i++) cudaFuncGetAttributes(&a, fns[i]);
+  cudaGetLastError();
+}
+void preload_sort_kernels() {
+  const void *const f[] = {(const void *)k_hash_count<false>, (const void *)k_scan_cells, (const void *)k_scatter,
+                           (const void *)k_rank_reorder<true>};
+  preload(f, sizeof f / sizeof f[0]);
+}

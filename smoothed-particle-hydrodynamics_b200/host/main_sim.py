@@ -3,8 +3,9 @@ restated for Python 3 (`n // 2`, lists instead of py2 `map` iterators; numpy opt
 
 muscle_simulation().run() returns 96 floats: two travelling sine waves sampled at 12 positions, each
 sample doubled to 24, concatenated [w1, w2, w2, w1]; `t` advances by 1.0 per call, phase velocity 1e-4.
-Parity is "unpinned by the reference" (it needs Python 2): pinned instead by the known-answer test in
-tests/test_host.py generated from this restatement.
+Parity: PINNED to the reference's own script — tests/golden/main_sim_kat.json holds the 96 doubles of calls
+0, 1, 2, 500 and 1000 produced by /root/reference/src/main_sim.py itself (run under Python 3 after two mechanical
+py2 -> py3 rewrites of an in-memory copy, tests/golden/make_main_sim_kat.py); tests/test_host.py compares exactly.
 """
 import math
 

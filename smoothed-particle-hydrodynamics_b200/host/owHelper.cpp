@@ -149,8 +149,10 @@ bool owHelper::loadMembranes(int *&membraneData_cpp, int &nMembranes, int *&pml,
 
 // buffers/position_buffer.txt: line 1 Ne, line 2 Nl, then one row "x\ty\tz\ttype" per NON-boundary particle per
 // saved frame; connection_buffer.txt: 32*Ne rows of 4 floats; membranes_buffer.txt: count, then rows.
-// Deviation (documented in DESIGN.md): the reference writes membranes[4*i+0..3] from a 3-stride array
-// (owHelper.cpp:1664-1665, out-of-bounds garbage); here each row is the triangle's 3 indices.
+// membranes_buffer.txt keeps the reference's row width of FOUR ints (owHelper.cpp:1664-1665 writes, :1724-1727
+// reads four per row) so that files travel between the two programs; the reference fills the rows from a 3-stride
+// array with index 4*i (rows shifted, the last quarter read out of bounds): here a row is the triangle's 3 indices
+// plus a 0 filler. The reader below accepts 3 or 4 columns.
 void owHelper::loadConfigurationToFile(float *position, float *connections, int *membranes, bool firstIteration) {
   try {
     ofstream positionFile;
@@ -180,7 +182,7 @@ void owHelper::loadConfigurationToFile(float *position, float *connections, int 
       membranesFile << numOfMembranes << "\n";
       if (membranes)
         for (int i = 0; i < numOfMembranes; i++)
-          membranesFile << membranes[3 * i + 0] << "\t" << membranes[3 * i + 1] << "\t" << membranes[3 * i + 2] << "\n";
+          membranesFile << membranes[3 * i + 0] << "\t" << membranes[3 * i + 1] << "\t" << membranes[3 * i + 2] << "\t" << 0 << "\n";
       membranesFile.close();
     }
   } catch (std::exception &e) {
@@ -227,7 +229,12 @@ void owHelper::loadConfigurationFromFile(float *&position, float *&connections, 
       if (membranesFile.is_open()) membranesFile >> m_count;
       numOfMembranes = m_count;
       membranes = new int[3 * m_count + 3];
-      for (i = 0; i < m_count && (membranesFile >> membranes[3 * i] >> membranes[3 * i + 1] >> membranes[3 * i + 2]); i++) {}
+      std::vector<int> tok;
+      for (int v; membranesFile >> v;) tok.push_back(v);
+      const int cols = (m_count > 0 && tok.size() >= (size_t)4 * m_count) ? 4 : 3;  // reference row width, or the 3-column files of round 1
+      for (i = 0; i < m_count && (size_t)(cols * i + 2) < tok.size(); i++) {
+        membranes[3 * i] = tok[cols * i]; membranes[3 * i + 1] = tok[cols * i + 1]; membranes[3 * i + 2] = tok[cols * i + 2];
+      }
     }
   } catch (std::exception &e) {
     std::cout << "ERROR: " << e.what() << std::endl;

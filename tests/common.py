@@ -122,9 +122,13 @@ def canon(name, a):
     return a
 
 
-def assert_same_state(ca, cb, buffers=ALL_STATE, tag=""):
+def assert_same_state(ca, cb, buffers=ALL_STATE, tag="", no_nan=False):
+    """no_nan: also require that neither side holds a NaN anywhere (first_mismatch lets any NaN match any NaN; the
+    fixture and bench scenes must never get there)."""
     for b in buffers:
         x, y = canon(b, ca.read(b)), canon(b, cb.read(b))
+        if no_nan and x.dtype == np.float32 and b != "neighborMap":
+            assert not np.isnan(x).any() and not np.isnan(y).any(), "%s: NaN in buffer %s" % (tag, b)
         mm = first_mismatch(x, y)
         assert mm is None, "%s: buffer %s differs: %s" % (tag, b, mm)
 
