@@ -267,6 +267,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
     c->graph_mode = gm ? atoi(gm) : -1;
     const char *ln = getenv("SPH_LANES");
     c->lanes = ln ? atoi(ln) : 0;
+    const char *pd = getenv("SPH_PDL");
+    c->pdl_mode = pd ? atoi(pd) : -1;
   }
   bool ok = true;
 #define A(x) ok = ok && ((e = (x)) == cudaSuccess)
@@ -342,6 +344,7 @@ static int check_launch(sph_ctx *c, bool sync) {
 int sph_stage(sph_ctx *c, int stage) {
   if (!c) return fail(SPH_E_INVALID, "null ctx");
   CU(cudaSetDevice(c->device));
+  c->pdl = false;
   switch (stage) {
     case SPH_STAGE_CLEAR_BUFFERS: launch_clear_neighbors(c); break;
     case SPH_STAGE_HASH_PARTICLES: launch_hash_count(c, true); break;
@@ -369,10 +372,12 @@ int sph_stage(sph_ctx *c, int stage) {
 // ---------------------------------------------------------------- fused step
 // Optional per-kernel timing with CUDA events on the context's own stream (bench.py roofline).
 enum { PK_HASH = 0, PK_SORT, PK_NEIGHBORS, PK_FORCES, PK_ELASTIC, PK_PREDICT_DENSITY, PK_PRESSURE_FORCE,
-       PK_PRESSURE_FORCE_INTEGRATE, PK_MEMBRANES, PK_COUNT };
+       PK_PRESSURE_FORCE_INTEGRATE, PK_MEMBRANES, PK_SLAB_RECORDS_, PK_SLAB_ABSORB_, PK_SLAB_HALO_, PK_COUNT };
+static_assert(PK_SLAB_RECORDS_ == PK_SLAB_RECORDS && PK_SLAB_ABSORB_ == PK_SLAB_ABSORB && PK_SLAB_HALO_ == PK_SLAB_HALO, "sph_ctx.h");
 static const char *const kProfNames[PK_COUNT] = {
     "hash_count", "sort(scan+scatter+rank_reorder)", "find_neighbors+density", "forces+predict0", "elastic",
-    "predict_density+correct_pressure", "pressure_force+predict", "pressure_force+integrate", "membranes"};
+    "predict_density+correct_pressure", "pressure_force+predict", "pressure_force+integrate", "membranes",
+    "slab:classify+deliver+wait_neighbours", "slab:absorb", "slab:halo_send+wait+recv"};
 
 struct ProfRec { int kind; cudaEvent_t a, b; };
 struct Profiler {
@@ -403,6 +408,22 @@ struct ProfScope {
     if (p) { cudaEventRecord(r.b, c->stream); p->recs.push_back(r); }
   }
 };
+
+}  // extern "C"
+
+// the same scope for the slab kernels of sph_slab.cu
+ProfMark prof_mark_begin(sph_ctx *c, int kind) {
+  ProfMark m; m.on = false;
+  Profiler *p = (Profiler *)c->profiler;
+  if (p) { m.on = true; m.kind = kind; m.a = p->get(); m.b = p->get(); cudaEventRecord(m.a, c->stream); }
+  return m;
+}
+void prof_mark_end(sph_ctx *c, ProfMark &m) {
+  Profiler *p = (Profiler *)c->profiler;
+  if (m.on && p) { cudaEventRecord(m.b, c->stream); ProfRec r; r.kind = m.kind; r.a = m.a; r.b = m.b; p->recs.push_back(r); }
+}
+
+extern "C" {
 
 // Membrane interaction + finalize of the fused step. Without a membrane list the kernel would only zero the
 // displacement half of `position` (clearMembraneBuffers) and add +0 (finalize): the integration kernel has
@@ -474,6 +495,9 @@ int sph_step(sph_ctx *c) {
   if (!c) return fail(SPH_E_INVALID, "null ctx");
   CU(cudaSetDevice(c->device));
   clear_upper_halves_if_dirty(c);
+  // programmatic dependent launches between the step's kernels: with the graph (small, launch-bound scenes) unless
+  // SPH_PDL says otherwise; never with per-kernel events in between
+  c->pdl = !c->profiler && !c->slab && (c->pdl_mode < 0 ? want_graph(c) : c->pdl_mode != 0);
   if (!want_graph(c)) {
     c->launches += step_body(c, 0);
     c->launches += step_body(c, 1);
@@ -483,7 +507,13 @@ int sph_step(sph_ctx *c) {
   // replay cannot carry sits between the two graphs: the wait for a pipelined read-back, and the once-per-upload
   // clearing of the displacement halves in front.
   if (c->stepGraph[0] && c->graphStream != c->stream) drop_graph(c);
+  if (!c->cellCountClean) {   // the captured step has no memset of the cell histogram: k_rank_reorder leaves it zeroed
+    CU(cudaMemsetAsync(c->cellCount, 0, sizeof(unsigned) * ((size_t)c->d.G + 1), c->stream));
+    c->cellCountClean = true;
+  }
+  if (c->stepGraph[0] && c->graphPdl != c->pdl) drop_graph(c);
   if (!c->stepGraph[0]) {
+    c->graphPdl = c->pdl;
     int rc = capture_half(c, 0);
     if (!rc) rc = capture_half(c, 1);
     if (rc) { drop_graph(c); return rc; }
@@ -508,6 +538,7 @@ int sph_step_part(sph_ctx *c, int part) {
   CU(cudaSetDevice(c->device));
   switch (part) {
     case 0:
+      c->pdl = false;
       clear_upper_halves_if_dirty(c);
       { ProfScope s(c, PK_HASH); launch_hash_count(c, false); }
       { ProfScope s(c, PK_SORT); launch_sort(c, true); }

@@ -79,6 +79,10 @@ struct sph_ctx {
   int graphNodes[2];           // kernels in each captured half
   int graph_mode;              // -1 = by size, 0 = never, 1 = always
   bool capturing;              // inside stream capture: launchers must not touch events of other streams
+  int pdl_mode;                // SPH_PDL: -1 = with the graph, 0 = never, 1 = always
+  bool graphPdl;               // the captured graphs were recorded with programmatic launches
+  bool pdl;                    // programmatic dependent launch between the kernels of the step (SPH_PDL=0|1, default: with the graph)
+  bool cellCountClean;         // the cell histogram is all zero (k_rank_reorder left it so): no memset before the next hash
   int lanes;                   // SPH_LANES: lanes per particle of the small-scene gather kernels (0 = by size)
   // pipelined read-back (sph_read_begin / sph_read_end): a device-to-host copy of position or velocity that
   // runs on its own stream while the next step computes; the integration kernel waits for it (read_fence)
@@ -98,11 +102,35 @@ struct sph_ctx {
   unsigned sigNext;
 };
 
+// Kernel launch of the fused step: with c->pdl the launch carries the programmatic-stream-serialization attribute
+// (see pdl_entry, sph_device.cuh), otherwise it is a plain launch.
+template <typename... KArgs, typename... Args>
+static inline void launch_k(sph_ctx *c, void (*kernel)(KArgs...), dim3 grid, dim3 block, Args &&...args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = c->stream;
+  cudaLaunchAttribute attr[1];
+  if (c->pdl) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // order the next writer of position / velocity after a pending pipelined read of them
 static inline void read_fence(sph_ctx *c) {
   if (c->readPending && !c->capturing) cudaStreamWaitEvent(c->stream, c->evReadDone, 0);
 }
 
+// per-kernel event timing (sph_profile_enable) for the slab kernels; defined in sph_capi.cu
+enum { PK_SLAB_RECORDS = 9, PK_SLAB_ABSORB = 10, PK_SLAB_HALO = 11 };
+struct ProfMark { int kind; cudaEvent_t a, b; bool on; };
+ProfMark prof_mark_begin(sph_ctx *c, int kind);
+void prof_mark_end(sph_ctx *c, ProfMark &m);
 // sph_sort.cu
 void launch_hash_count(sph_ctx *c, bool write_pairs);
 void launch_sort(sph_ctx *c, bool fuse_reorder);   // scan + scatter + rank (+ reorder)

@@ -48,6 +48,15 @@ struct DevParams {
   float d2H, d2Close;
 };
 
+// Programmatic dependent launch (sm_90+): first statement of every kernel of the fused step. launch_dependents lets
+// the NEXT kernel of the stream be scheduled as soon as all CTAs of this one are resident, so its launch latency and
+// ramp-up overlap this kernel's tail; wait blocks until the PREVIOUS kernel has completed and its writes are visible
+// (transitively: it passed its own wait). Both are no-ops for launches without the programmatic attribute.
+__device__ __forceinline__ void pdl_entry() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- float4 lane-wise helpers (OpenCL vector semantics, one IEEE op per lane) ----
 __device__ __forceinline__ float4 f4(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
 __device__ __forceinline__ float4 operator+(float4 a, float4 b) { return f4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }

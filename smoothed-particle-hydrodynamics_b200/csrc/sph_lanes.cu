@@ -32,6 +32,7 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
                                                              float4 *__restrict__ recB) {
   using G = LaneGeom<L>;
   __shared__ float term[6 * G::CS];
+  pdl_entry();
   const int t = threadIdx.x, pl = t / L, l = t % L;
   const int id = blockIdx.x * G::P + pl;
   const bool live = id < d.N;
@@ -101,6 +102,7 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_predict_density_lanes(DevPar
                                                                       float4 *__restrict__ recB) {
   using G = LaneGeom<L>;
   __shared__ float term[G::CS];
+  pdl_entry();
   const int t = threadIdx.x, pl = t / L, l = t % L;
   const int id = blockIdx.x * G::P + pl;
   const bool live = id < d.N;
@@ -151,6 +153,7 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevPara
                                                                      int *__restrict__ memList, int *__restrict__ memCount) {
   using G = LaneGeom<L>;
   __shared__ float term[3 * G::CS];
+  pdl_entry();
   const int t = threadIdx.x, pl = t / L, l = t % L;
   const int id = blockIdx.x * G::P + pl;
   const bool live = id < d.N;
@@ -227,9 +230,9 @@ template <int L> static inline int lanes_grid(int n) { return (n + LaneGeom<L>::
 bool launch_forces_lanes(sph_ctx *c, int L) {
   float4 *pred = c->sortedPosition + c->d.N;
 #define F_ARGS c->d, c->sortedPosition, c->sortedVelocity, c->sortedType, c->nbIds, c->rho, c->acceleration, c->pressure, pred, c->recA, c->recB
-  if (L == 4) k_forces_lanes<4><<<lanes_grid<4>(c->d.N), LaneGeom<4>::T, 0, c->stream>>>(F_ARGS);
-  else if (L == 8) k_forces_lanes<8><<<lanes_grid<8>(c->d.N), LaneGeom<8>::T, 0, c->stream>>>(F_ARGS);
-  else if (L == 16) k_forces_lanes<16><<<lanes_grid<16>(c->d.N), LaneGeom<16>::T, 0, c->stream>>>(F_ARGS);
+  if (L == 4) launch_k(c, k_forces_lanes<4>, dim3(lanes_grid<4>(c->d.N)), dim3(LaneGeom<4>::T), F_ARGS);
+  else if (L == 8) launch_k(c, k_forces_lanes<8>, dim3(lanes_grid<8>(c->d.N)), dim3(LaneGeom<8>::T), F_ARGS);
+  else if (L == 16) launch_k(c, k_forces_lanes<16>, dim3(lanes_grid<16>(c->d.N)), dim3(LaneGeom<16>::T), F_ARGS);
   else return false;
 #undef F_ARGS
   return true;
@@ -238,9 +241,9 @@ bool launch_forces_lanes(sph_ctx *c, int L) {
 bool launch_predict_density_lanes(sph_ctx *c, int L) {
   const float4 *pred = c->sortedPosition + c->d.N;
 #define D_ARGS c->d, pred, c->nbIds, c->rho, c->pressure, c->recB
-  if (L == 4) k_predict_density_lanes<4><<<lanes_grid<4>(c->d.N), LaneGeom<4>::T, 0, c->stream>>>(D_ARGS);
-  else if (L == 8) k_predict_density_lanes<8><<<lanes_grid<8>(c->d.N), LaneGeom<8>::T, 0, c->stream>>>(D_ARGS);
-  else if (L == 16) k_predict_density_lanes<16><<<lanes_grid<16>(c->d.N), LaneGeom<16>::T, 0, c->stream>>>(D_ARGS);
+  if (L == 4) launch_k(c, k_predict_density_lanes<4>, dim3(lanes_grid<4>(c->d.N)), dim3(LaneGeom<4>::T), D_ARGS);
+  else if (L == 8) launch_k(c, k_predict_density_lanes<8>, dim3(lanes_grid<8>(c->d.N)), dim3(LaneGeom<8>::T), D_ARGS);
+  else if (L == 16) launch_k(c, k_predict_density_lanes<16>, dim3(lanes_grid<16>(c->d.N)), dim3(LaneGeom<16>::T), D_ARGS);
   else return false;
 #undef D_ARGS
   return true;
@@ -250,7 +253,7 @@ bool launch_pressure_force_lanes(sph_ctx *c, int mode, int L) {
   float4 *pred = c->sortedPosition + c->d.N;
 #define P_ARGS c->d, c->spT, c->sortedVelocity, c->nbIds, c->recB, c->acceleration, c->sortedPosition, pred, c->particleIndex, \
                c->position, c->velocity, c->elasticMask, c->memList, c->memCount
-#define P_LAUNCH(M, LL) k_pressure_force_lanes<M, LL><<<lanes_grid<LL>(c->d.N), LaneGeom<LL>::T, 0, c->stream>>>(P_ARGS)
+#define P_LAUNCH(M, LL) launch_k(c, k_pressure_force_lanes<M, LL>, dim3(lanes_grid<LL>(c->d.N)), dim3(LaneGeom<LL>::T), P_ARGS)
   if (mode != 1 && mode != 2) return false;
   if (L == 4) { if (mode == 1) P_LAUNCH(1, 4); else P_LAUNCH(2, 4); }
   else if (L == 8) { if (mode == 1) P_LAUNCH(1, 8); else P_LAUNCH(2, 8); }

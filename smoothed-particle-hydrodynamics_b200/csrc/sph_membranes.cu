@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(ML_THREADS) k_membrane_lanes(DevParams d, floa
   __shared__ float4 sNw[ML_P][SPH_NB];
   __shared__ float sW[ML_P][SPH_NB + 1], sW2[ML_P][SPH_NB + 1];
   __shared__ unsigned char sKind[ML_P][SPH_NB + 4];
+  pdl_entry();
   const int t = threadIdx.x, pl = t / ML_L, l = t % ML_L;
   const int item = blockIdx.x * ML_P + pl;
   const bool live = item < *memCount;
@@ -194,6 +195,7 @@ __global__ void __launch_bounds__(ML_THREADS) k_membrane_lanes(DevParams d, floa
 __global__ void __launch_bounds__(256) k_membrane_finalize_fused(DevParams d, float4 *__restrict__ position,
                                                                  const uint2 *__restrict__ particleIndex,
                                                                  const float *__restrict__ sortedType, int *memCount) {
+  pdl_entry();
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id == 0) *memCount = 0;
   if (id >= d.N) return;
@@ -225,11 +227,10 @@ void launch_membrane_interaction(sph_ctx *c, bool fuse_finalize) {
   if (fuse_finalize && pml) {
     // the reference's memset race (k_membrane_finalize_fused resets *memCount after the lanes kernel has read it) is
     // ordered by the stream: lanes kernel, then finalize kernel
-    k_membrane_lanes<<<(c->d.N + ML_P - 1) / ML_P, ML_THREADS, 0, c->stream>>>(c->d, c->position, c->particleIndex, c->sortedType,
-                                                                               c->nbIds, pml, c->membraneData, c->elasticMask,
-                                                                               c->memList, c->memCount);
-    k_membrane_finalize_fused<<<(c->d.N + 255) / 256, 256, 0, c->stream>>>(c->d, c->position, c->particleIndex, c->sortedType,
-                                                                           c->memCount);
+    launch_k(c, k_membrane_lanes, dim3((c->d.N + ML_P - 1) / ML_P), dim3(ML_THREADS), c->d, c->position, c->particleIndex,
+             c->sortedType, c->nbIds, pml, c->membraneData, c->elasticMask, c->memList, c->memCount);
+    launch_k(c, k_membrane_finalize_fused, dim3((c->d.N + 255) / 256), dim3(256), c->d, c->position, c->particleIndex,
+             c->sortedType, c->memCount);
   } else {
     k_membrane_interaction<<<(c->d.N + 127) / 128, 128, 0, c->stream>>>(c->d, c->position, c->particleIndex, c->sortedType,
                                                                         c->nbIds, pml, c->membraneData);

@@ -156,6 +156,7 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
                                                                 const unsigned *__restrict__ cellStart,
                                                                 int *__restrict__ nb, float *__restrict__ rho,
                                                                 float4 *__restrict__ recA) {
+  pdl_entry();
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= d.N) return;
   find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
@@ -205,6 +206,7 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
 // 256-bit loads of a sweep pass share one address computation.
 __global__ void __launch_bounds__(256) k_soa_positions(int n, const float4 *__restrict__ sp, float *__restrict__ S) {
+  pdl_entry();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   float *o = S + 24 * (size_t)(i >> 3) + (i & 7);
   if (i < n) {
@@ -228,6 +230,7 @@ __device__ __forceinline__ float3 cell_local_h(const DevParams &d, const float4 
 }
 __global__ void __launch_bounds__(256) k_soa_positions_half(DevParams d, const float4 *__restrict__ sp,
                                                             __half *__restrict__ S) {
+  pdl_entry();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int s = i & 15;
   __half *o = S + 48 * (size_t)(i >> 4) + 2 * (s & 7) + (s >> 3);
@@ -256,6 +259,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   __shared__ int binCount[64], binBase[64];
   __shared__ int binTot0;
   __shared__ unsigned char srcOf[LP_THREADS];
+  pdl_entry();
   const int tid = threadIdx.x;
   // Lanes that share (cell, octant) walk the same cells in lockstep and load the same addresses. The CTA's 128
   // consecutive particles (about two cells) are therefore dealt to the threads grouped by (cell, octant): a counting
@@ -474,23 +478,31 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   // smaller r_thr: the exact distances are gathered once for most lanes.
   const float r2open = ((float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS) *
                        ((float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS);
+  auto hist_add = [&](float dd) {
+    float sq;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
+    int e = min((int)(sq * d.binScale), SPH_RADIUS_SEGMENTS);
+    const int bin = e + ((dd >= d.binT[e + 1]) ? 1 : 0) - ((dd < d.binT[e]) ? 1 : 0);
+    if (bin < SPH_RADIUS_SEGMENTS) {
+      const int w = bin >> 3;
+      const unsigned long long inc = 1ull << ((bin & 7) * 7);
+      hist0 += (w == 0) ? inc : 0ull;
+      hist1 += (w == 1) ? inc : 0ull;
+      hist2 += (w == 2) ? inc : 0ull;
+      hist3 += (w == 3) ? inc : 0ull;
+    }
+  };
+  // VAR 2 only COUNTS the candidates within h in the first pass: with fewer than 32 of them the running sum of the
+  // radial histogram never reaches 32 and r_thr keeps its largest value whatever the bins are (sphFluid.cl:310-324),
+  // so the histogram is built (in a pass of its own) only for the particles that have 32 or more — none or few in a
+  // fluid near rest density, all in a compressed one.
+  int within = 0;
   auto first_pass = [&](unsigned hv) {
     const int j = hit_index(hv);
     if (j == id) return;
     const float dd = dist2(j);
     if (dd <= h2) {
-      float sq;
-      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(dd));
-      int e = min((int)(sq * d.binScale), SPH_RADIUS_SEGMENTS);
-      const int bin = e + ((dd >= d.binT[e + 1]) ? 1 : 0) - ((dd < d.binT[e]) ? 1 : 0);
-      if (bin < SPH_RADIUS_SEGMENTS) {
-        const int w = bin >> 3;
-        const unsigned long long inc = 1ull << ((bin & 7) * 7);
-        hist0 += (w == 0) ? inc : 0ull;
-        hist1 += (w == 1) ? inc : 0ull;
-        hist2 += (w == 2) ? inc : 0ull;
-        hist3 += (w == 3) ? inc : 0ull;
-      }
+      if (VAR == 2) within++; else hist_add(dd);
     }
     if (dd <= r2open && found < SPH_NB) take(j, dd);
   };
@@ -511,6 +523,16 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   };
   if (VAR == 2) {
     for (int t = 0; t < n; t++) first_pass(next_hit());
+    if (within >= SPH_NB) {   // the histogram decides r_thr: build it
+      curMask = 0u;
+      curEntry = 0;
+      for (int t = 0; t < n; t++) {
+        const int j = hit_index(next_hit());
+        if (j == id) continue;
+        const float dd = dist2(j);
+        if (dd <= h2) hist_add(dd);
+      }
+    }
   } else {
     const int nList = min(n, LP_CAP);
     for (int t = 0; t < nList; t++) first_pass(hits[t][tid]);
@@ -572,7 +594,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
 #define CP_CAP 128
 
 template <bool WITH_DENSITY>
-__global__ void __launch_bounds__(CP_THREADS) k_find_neighbors_coop(DevParams d, const float4 *__restrict__ sp,
+__global__ void __launch_bounds__(CP_THREADS, 3) k_find_neighbors_coop(DevParams d, const float4 *__restrict__ sp,
                                                                     const float *__restrict__ S,
                                                                     const unsigned *__restrict__ cellStart,
                                                                     int *__restrict__ nb, float *__restrict__ rho,
@@ -580,6 +602,7 @@ __global__ void __launch_bounds__(CP_THREADS) k_find_neighbors_coop(DevParams d,
   __shared__ int hitJ[CP_P][CP_CAP + 1];      // sorted index of hit t (odd row stride)
   __shared__ float hitD[CP_P][CP_CAP + 1];    // its exact squared distance
   __shared__ float rhoT[CP_P][SPH_NB + 1];    // rho(t) term of the neighbour in slot s
+  pdl_entry();
   const int t = threadIdx.x, pl = t / CP_L, l = t % CP_L;
   const int id = blockIdx.x * CP_P + pl;
   const bool live = id < d.N;
@@ -1322,23 +1345,23 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
                         span < (long long)c->d.mask + 1;
     const int var = (c->list_variant == 2 && !halfOk) ? 1 : c->list_variant;
     if (var == 2)
-      k_soa_positions_half<<<(n + 32 + 255) / 256, 256, 0, c->stream>>>(c->d, c->sortedPosition, reinterpret_cast<__half *>(c->soa));
+      launch_k(c, k_soa_positions_half, dim3((n + 32 + 255) / 256), dim3(256), c->d, c->sortedPosition, reinterpret_cast<__half *>(c->soa));
     else
-      k_soa_positions<<<(n + 16 + 255) / 256, 256, 0, c->stream>>>(n, c->sortedPosition, c->soa);
+      launch_k(c, k_soa_positions, dim3((n + 16 + 255) / 256), dim3(256), n, c->sortedPosition, c->soa);
     // small scenes: eight lanes per particle (SPH_NEIGHBOR_PATH=coop forces it at any size, =list forbids it)
     const bool coop = var == 2 && (c->force_coop_neighbors || (!c->force_list_neighbors && n <= SPH_COOP_MAX_N));
     if (coop) {
       const int cb = (n + CP_P - 1) / CP_P;
       if (with_density)
-        k_find_neighbors_coop<true><<<cb, CP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, c->rho, c->recA);
+        launch_k(c, k_find_neighbors_coop<true>, dim3(cb), dim3(CP_THREADS), c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, c->rho, c->recA);
       else
-        k_find_neighbors_coop<false><<<cb, CP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, c->rho, nullptr);
+        launch_k(c, k_find_neighbors_coop<false>, dim3(cb), dim3(CP_THREADS), c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, c->rho, (float4 *)nullptr);
       return;
     }
     const int blocks = (n + LP_THREADS - 1) / LP_THREADS;
 #define LP_LAUNCH(WD, V, REC)                                                                                      \
-  k_find_neighbors_list<WD, V><<<blocks, LP_THREADS, 0, c->stream>>>(c->d, c->sortedPosition, c->soa, c->cellStart, c->nbIds, \
-                                                                     c->rho, REC)
+  launch_k(c, k_find_neighbors_list<WD, V>, dim3(blocks), dim3(LP_THREADS), c->d, c->sortedPosition, c->soa, c->cellStart, \
+           c->nbIds, c->rho, (float4 *)(REC))
     if (var == 0) { if (with_density) LP_LAUNCH(true, 0, c->recA); else LP_LAUNCH(false, 0, nullptr); }
     else if (var == 1) { if (with_density) LP_LAUNCH(true, 1, c->recA); else LP_LAUNCH(false, 1, nullptr); }
     else { if (with_density) LP_LAUNCH(true, 2, c->recA); else LP_LAUNCH(false, 2, nullptr); }
@@ -1348,9 +1371,9 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
   if (!useTiles) {
     int blocks = (c->d.N + 127) / 128;
     if (with_density)
-      k_find_neighbors_generic<true><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho, c->recA);
+      launch_k(c, k_find_neighbors_generic<true>, dim3(blocks), dim3(128), c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho, c->recA);
     else
-      k_find_neighbors_generic<false><<<blocks, 128, 0, c->stream>>>(c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho, nullptr);
+      launch_k(c, k_find_neighbors_generic<false>, dim3(blocks), dim3(128), c->d, c->sortedPosition, c->cellStart, c->nbIds, c->rho, (float4 *)nullptr);
     return;
   }
   // persistent CTAs (one resident wave); home blocks handed out through an atomic cursor over cellList

@@ -12,6 +12,7 @@
 //
 // The library packs and unpacks; moving bytes between ranks is the caller's business (torch.distributed /
 // NCCL in slab.py, device-to-device copies in the single-process tests).
+#include <stdlib.h>
 #include <string.h>
 
 #include "sph_ctx.h"
@@ -354,9 +355,11 @@ void slab_destroy(sph_ctx *c) {
 // i.e. after the neighbour consumed everything of step k.
 #define SLAB_SLOTS 16
 struct SlabMailHeader {
-  unsigned flag[2][SLAB_SLOTS];
-  int counts[2][2];   // [origin side]{migrants, ghosts} of the current step
-  unsigned pad[28];
+  unsigned flag[2][SLAB_SLOTS];   // [origin side][1 + e] = epoch of the last complete halo delivery e
+  // [origin side][0 = migrants, 1 = ghosts] record delivery of a step: epoch << 32 | count in ONE 64-bit word each,
+  // so that a count and its flag arrive together and no fence is needed between them
+  unsigned long long records[2][2];
+  unsigned pad[24];
 };
 static_assert(sizeof(SlabMailHeader) == 256, "mailbox header");
 
@@ -380,19 +383,39 @@ __device__ __forceinline__ unsigned long long global_ns() {
   return t;
 }
 
-// Wait until *flag has reached `epoch` (wrap-safe). Gives up after 10 s and raises the sticky error word *err: a lost
-// neighbour must not hang the GPU.
-__device__ __forceinline__ void wait_delivery(const volatile unsigned *flag, unsigned epoch, int *err) {
+// Wait until *flag has reached `epoch` (wrap-safe), with acquire semantics at system scope: the data the neighbour
+// wrote before it raised the flag is visible to the loads that follow. No __threadfence_system() anywhere on this
+// path: a system-scope fence waits for the device's outstanding PCIe traffic too, and with a 130 MB device-to-host
+// read-back in flight (the pipelined e2e loop) every fence cost ~70 us — 2.1 ms per step when each of the classify
+// kernel's 32 k blocks fenced (tools/fence_probe.py). Gives up after 10 s and raises the sticky error word *err: a
+// lost neighbour must not hang the GPU.
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys(unsigned *p, unsigned v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void wait_delivery(const unsigned *flag, unsigned epoch, int *err) {
   const unsigned long long t0 = global_ns();
-  while ((int)(*flag - epoch) < 0) {
+  while ((int)(ld_acquire_sys(flag) - epoch) < 0) {
     __nanosleep(200);
     if (global_ns() - t0 > 10000000000ull) { atomicOr(err, 256); break; }
   }
-  __threadfence_system();
 }
 
-// classify of the linked step: k_slab_classify writing into the neighbours' mailboxes, then — last block — the
-// counts and the delivery flag of slot 0, and this rank's own counters to pinned host memory.
+// classify of the linked step: k_slab_classify writing into the neighbours' mailboxes. The delivery is announced by
+// the NEXT kernel of the stream (k_slab_records): a kernel boundary orders all of this kernel's writes — peer memory
+// included — before anything the next kernel does, so no fence is needed here.
 struct SlabLinkOut {
   SlabRec *mig[2], *ghost[2], *migLocal[2];  // [0] = towards rank-1, [1] = towards rank+1
   SlabMailHeader *hdr[2];
@@ -404,12 +427,32 @@ __global__ void __launch_bounds__(256) k_slab_classify_linked(DevParams d, SlabG
                                                               const unsigned *__restrict__ gid, float4 *__restrict__ posN,
                                                               float4 *__restrict__ velN, unsigned *__restrict__ gidN,
                                                               int *__restrict__ listD, int *__restrict__ listU,
-                                                              int *counters, volatile int *hostCounters) {
+                                                              int *counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  // Kept particles are compacted in BLOCK ORDER (one atomic per block, ranks inside the block by ballot): the arrays
+  // keep the locality of the previous step's order, which the sort's gathers and histogram atomics live on (a
+  // per-thread atomic scrambled it: sort 0.48 -> 0.62 ms, neighbour search + 0.05 ms at 8 M particles).
+  __shared__ int warpKept[8], blockBase;
+  float4 p = f4(0.f, 0.f, 0.f, 0.f), v = p;
+  unsigned g = 0u;
+  int cz = 0;
+  bool keep = false;
   if (i < s.nOwn) {
-    const float4 p = pos[i], v = vel[i];
-    const unsigned g = gid[i];
-    const int cz = (int)(p.z * d.cellSizeInv);
+    p = pos[i]; v = vel[i]; g = gid[i];
+    cz = (int)(p.z * d.cellSizeInv);
+    keep = !((s.hasDown && cz < s.z0) || (s.hasUp && cz >= s.z1));
+  }
+  const unsigned kmask = __ballot_sync(0xffffffffu, keep);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) warpKept[warp] = __popc(kmask);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int tot = 0;
+    for (int w = 0; w < 8; w++) { const int c = warpKept[w]; warpKept[w] = tot; tot += c; }
+    blockBase = tot ? atomicAdd(&counters[4], tot) : 0;
+  }
+  __syncthreads();
+  if (i < s.nOwn) {
     SlabRec r;
     r.pos = p; r.vel = v; r.tag = make_float4(__uint_as_float(g), 0.f, 0.f, 0.f);
     if ((s.hasDown && cz < s.z0 - 1 - s.slack) || (s.hasUp && cz > s.z1 + s.slack)) atomicOr(&counters[5], 1);
@@ -420,7 +463,7 @@ __global__ void __launch_bounds__(256) k_slab_classify_linked(DevParams d, SlabG
       const int slot = atomicAdd(&counters[2], 1);
       if (slot < s.migCap) { o.mig[1][slot] = r; o.migLocal[1][slot] = r; } else atomicOr(&counters[5], 2);
     } else {
-      const int ni = atomicAdd(&counters[4], 1);
+      const int ni = blockBase + warpKept[warp] + __popc(kmask & ((1u << lane) - 1u));
       posN[ni] = p; velN[ni] = v; gidN[ni] = g;
       if (s.hasDown && cz == s.z0) {
         const int slot = atomicAdd(&counters[1], 1);
@@ -432,64 +475,52 @@ __global__ void __launch_bounds__(256) k_slab_classify_linked(DevParams d, SlabG
       }
     }
   }
-  // last block: everything every block wrote (also into peer memory) is ordered before the flags
-  __shared__ int last;
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(&counters[7], 1) == (int)gridDim.x - 1;
-  __syncthreads();
-  if (!last) return;
-  __threadfence_system();
-  if (threadIdx.x < 8) hostCounters[threadIdx.x] = ((volatile int *)counters)[threadIdx.x];
-  if (threadIdx.x < 2 && o.hdr[threadIdx.x]) {
-    const int side = threadIdx.x;            // towards rank-1 (0) or rank+1 (1); it arrives there from the other side
-    const int from = 1 - side;
-    SlabMailHeader *h = o.hdr[side];
-    const int mig = min(((volatile int *)counters)[2 * side], s.migCap), gh = min(((volatile int *)counters)[2 * side + 1], s.haloCap);
-    ((volatile int *)h->counts[from])[0] = mig;
-    ((volatile int *)h->counts[from])[1] = gh;
-    __threadfence_system();
-    ((volatile unsigned *)h->flag[from])[0] = o.epoch;
-  }
 }
 
-// Wait for the neighbours' record deliveries of this step and hand their counts to the host (pinned, [8..11]).
-__global__ void k_slab_wait_records(SlabMailHeader *mine, int hasDown, int hasUp, unsigned epoch, int *counters,
-                                    volatile int *hostCounters, int *sticky) {
-  const int f = threadIdx.x;  // origin side
-  if (f < 2) {
-    const bool has = f == 0 ? hasDown : hasUp;
-    int mig = 0, gh = 0;
-    if (has) {
-      wait_delivery(&mine->flag[f][0], epoch, sticky);
-      mig = ((volatile int *)mine->counts[f])[0];
-      gh = ((volatile int *)mine->counts[f])[1];
+// After k_slab_classify_linked: announce this rank's record deliveries (counts + epoch in one word per neighbour),
+// wait for the neighbours' announcements, and hand all counts to the host (pinned memory: [0..7] own counters,
+// [8..11] incoming {mig from below, ghosts from below, mig from above, ghosts from above}, [5] error bits, [6] sticky).
+__global__ void k_slab_records(SlabMailHeader *mine, SlabMailHeader *down, SlabMailHeader *up, unsigned epoch, int migCap,
+                               int haloCap, const int *counters, volatile int *hostCounters, int *sticky) {
+  const int t = threadIdx.x;
+  if (t < 4) {   // t = 2 * side + kind: towards rank-1 (it arrives there from above = origin side 1) / rank+1
+    SlabMailHeader *h = (t >> 1) == 0 ? down : up;
+    if (h) {
+      const unsigned n = (unsigned)min(counters[t], (t & 1) ? haloCap : migCap);
+      st_relaxed_sys64(&h->records[1 - (t >> 1)][t & 1], ((unsigned long long)epoch << 32) | n);
     }
-    hostCounters[8 + 2 * f] = mig;
-    hostCounters[9 + 2 * f] = gh;
   }
+  if (t < 4) {   // t = 2 * origin side + kind
+    const bool has = (t >> 1) == 0 ? down != nullptr : up != nullptr;
+    int n = 0;
+    if (has) {
+      const unsigned long long t0 = global_ns();
+      unsigned long long w;
+      while ((int)((unsigned)((w = ld_acquire_sys64(&mine->records[t >> 1][t & 1])) >> 32) - epoch) < 0) {
+        __nanosleep(200);
+        if (global_ns() - t0 > 10000000000ull) { atomicOr(sticky, 256); break; }
+      }
+      n = (int)(unsigned)w;
+    }
+    hostCounters[8 + t] = n;
+  }
+  if (t < 8) hostCounters[t] = counters[t];
   __syncwarp();
-  if (threadIdx.x == 0) {
-    hostCounters[5] = ((volatile int *)counters)[5];
-    hostCounters[6] = *(volatile int *)sticky;   // a delivery of this or an earlier step timed out
-  }
-  __threadfence_system();
+  if (t == 0) hostCounters[6] = *(volatile int *)sticky;   // a delivery of this or an earlier step timed out
 }
 
 // Halo refresh, sending half: gather `FIELD` of the particles the two neighbours hold as ghosts and store the values
-// into the neighbours' mailboxes; the last block to finish raises both delivery flags.
+// into the neighbours' mailboxes. The delivery flags are raised by the kernel that follows (k_slab_halo_recv).
 struct SlabHaloSend {
   int n[2];                 // values towards rank-1, rank+1
   const int *list[2];       // local original indices
   void *dst[2];             // halo buffer (this exchange's parity) in the neighbour's mailbox
-  volatile unsigned *flag[2];
-  unsigned epoch;
 };
 
 template <int FIELD>
 __global__ void __launch_bounds__(256) k_slab_halo_send(SlabHaloSend a, const unsigned *__restrict__ back,
                                                         const float *__restrict__ rho, const float4 *__restrict__ recB,
-                                                        const float4 *__restrict__ spPred, int *doneCounter) {
+                                                        const float4 *__restrict__ spPred) {
   const int total = a.n[0] + a.n[1];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int side = i < a.n[0] ? 0 : 1;
@@ -499,22 +530,14 @@ __global__ void __launch_bounds__(256) k_slab_halo_send(SlabHaloSend a, const un
     if (FIELD == 1) { const float4 q = recB[2 * (size_t)sid + 1]; ((float2 *)a.dst[side])[k] = make_float2(q.x, q.y); }
     if (FIELD == 2) ((float4 *)a.dst[side])[k] = spPred[sid];
   }
-  __shared__ int last;
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(doneCounter, 1) == (int)gridDim.x - 1;
-  __syncthreads();
-  if (!last) return;
-  __threadfence_system();
-  if (threadIdx.x < 2 && a.flag[threadIdx.x]) *a.flag[threadIdx.x] = a.epoch;
-  if (threadIdx.x == 0) *doneCounter = 0;  // ready for the next send (stream-ordered after this kernel)
 }
 
 // Receiving half: wait for the deliveries, scatter the values into the local ghosts.
 struct SlabHaloRecv {
   int n[2], first[2];             // ghosts received from rank-1, rank+1: counts and first local original index
   const void *src[2];             // halo buffer (this exchange's parity) in this rank's mailbox
-  const volatile unsigned *flag[2];
+  const unsigned *flag[2];        // this rank's delivery flags of the exchange
+  unsigned *raise[2];             // the neighbours' flags for what k_slab_halo_send (the previous kernel) stored there
   unsigned epoch;
 };
 
@@ -523,6 +546,8 @@ __global__ void __launch_bounds__(256) k_slab_halo_recv(SlabHaloRecv a, const un
                                                         float *__restrict__ rho, float4 *__restrict__ recA,
                                                         float4 *__restrict__ recB, float4 *__restrict__ spPred,
                                                         int *sticky) {
+  // the send kernel has completed (stream order): its stores are out, announce them; then wait for the neighbours'
+  if (blockIdx.x == 0 && threadIdx.x < 2 && a.raise[threadIdx.x]) st_relaxed_sys(a.raise[threadIdx.x], a.epoch);
   if (threadIdx.x < 2 && a.flag[threadIdx.x]) wait_delivery(a.flag[threadIdx.x], a.epoch, sticky);
   __syncthreads();
   const int total = a.n[0] + a.n[1];
@@ -557,7 +582,7 @@ static void preload_step_kernels() {
   preload_neighbor_kernels();
   preload_pcisph_kernels();
   preload_membrane_kernels();
-  const void *const f[] = {(const void *)k_slab_classify_linked, (const void *)k_slab_wait_records, (const void *)k_slab_append,
+  const void *const f[] = {(const void *)k_slab_classify_linked, (const void *)k_slab_records, (const void *)k_slab_append,
                            (const void *)k_slab_iota, (const void *)k_slab_halo_send<0>, (const void *)k_slab_halo_send<1>,
                            (const void *)k_slab_halo_send<2>, (const void *)k_slab_halo_recv<0>, (const void *)k_slab_halo_recv<1>,
                            (const void *)k_slab_halo_recv<2>};
@@ -652,11 +677,13 @@ int sph_slab_step_begin(sph_ctx *c) {
     o.migLocal[side] = s->migLocal[side];
   }
   o.epoch = s->epoch;
+  ProfMark pm = prof_mark_begin(c, PK_SLAB_RECORDS);
   k_slab_classify_linked<<<nblk(s->nOwn), 256, 0, c->stream>>>(c->d, g, o, c->position, c->velocity, s->gid, s->posAlt,
                                                                s->velAlt, s->gidAlt, s->sendList[0], s->sendList[1],
-                                                               s->counters, s->hostCountersDev);
-  k_slab_wait_records<<<1, 32, 0, c->stream>>>((SlabMailHeader *)s->mail, s->hasDown, s->hasUp, s->epoch, s->counters,
-                                               s->hostCountersDev, s->doneCounter + 1);
+                                                               s->counters);
+  k_slab_records<<<1, 32, 0, c->stream>>>((SlabMailHeader *)s->mail, o.hdr[0], o.hdr[1], s->epoch, s->migCap, s->haloCap,
+                                          s->counters, s->hostCountersDev, s->doneCounter + 1);
+  prof_mark_end(c, pm);
   SCU(cudaGetLastError());
   s->stepOpen = true;
   return 0;
@@ -676,18 +703,20 @@ static int linked_halo(sph_ctx *c, int field) {
     a.n[side] = has ? s->nSend[side] : 0;
     a.list[side] = s->sendList[side];
     a.dst[side] = has ? (void *)(s->peer[side] + m.halo[from][par]) : nullptr;
-    a.flag[side] = has ? &((SlabMailHeader *)s->peer[side])->flag[from][1 + e] : nullptr;
+    b.raise[side] = has ? &((SlabMailHeader *)s->peer[side])->flag[from][1 + e] : nullptr;
     b.n[side] = has ? s->nRecv[side] : 0;
     b.first[side] = s->recvStart[side];
     b.src[side] = s->mail + m.halo[side][par];
     b.flag[side] = has ? &((SlabMailHeader *)s->mail)->flag[side][1 + e] : nullptr;
   }
-  a.epoch = b.epoch = s->epoch;
+  b.epoch = s->epoch;
   float4 *pred = c->sortedPosition + c->d.N;
   const int gs = min(nblk(a.n[0] + a.n[1]), 4 * c->numSMs), gr = min(nblk(b.n[0] + b.n[1]), 4 * c->numSMs);
-#define SEND(F) k_slab_halo_send<F><<<gs, 256, 0, c->stream>>>(a, c->particleIndexBack, c->rho, c->recB, pred, s->doneCounter)
+#define SEND(F) k_slab_halo_send<F><<<gs, 256, 0, c->stream>>>(a, c->particleIndexBack, c->rho, c->recB, pred)
 #define RECV(F) k_slab_halo_recv<F><<<gr, 256, 0, c->stream>>>(b, c->particleIndexBack, c->rho, c->recA, c->recB, pred, s->doneCounter + 1)
+  ProfMark pm = prof_mark_begin(c, PK_SLAB_HALO);
   if (field == 0) { SEND(0); RECV(0); } else if (field == 1) { SEND(1); RECV(1); } else { SEND(2); RECV(2); }
+  prof_mark_end(c, pm);
 #undef SEND
 #undef RECV
   c->launches += 2;
@@ -713,7 +742,9 @@ int sph_slab_step_end(sph_ctx *c) {
   s->migOut[0] = h[0]; s->ghostOut[0] = h[1]; s->migOut[1] = h[2]; s->ghostOut[1] = h[3];
   s->myMig[0] = s->migLocal[0]; s->myMig[1] = s->migLocal[1];
   const int incoming[4] = {h[8], h[9], h[10], h[11]};
+  ProfMark pm = prof_mark_begin(c, PK_SLAB_ABSORB);
   int rc = sph_slab_absorb(c, s->mail + m.mig[0], s->mail + m.ghost[0], s->mail + m.mig[1], s->mail + m.ghost[1], incoming);
+  prof_mark_end(c, pm);
   if (rc) return rc;
   c->launches += 5;
   const int iters = c->p.max_iteration < 1 ? 1 : c->p.max_iteration;

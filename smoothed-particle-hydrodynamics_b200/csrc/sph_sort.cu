@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(256) k_hash_count(DevParams d, const float4 *_
                                                     uint2 *__restrict__ particleIndex,
                                                     unsigned long long *__restrict__ scanState,
                                                     unsigned *__restrict__ scanTicket, int scanTiles) {
+  pdl_entry();
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   // reset the look-back scan of this step's sort (k_scan_cells runs after this kernel): the step's launch
   // parameters are then the same every step, which is what lets sph_step replay a captured CUDA graph
@@ -60,6 +61,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_cells(unsigned *__restric
   __shared__ unsigned s_tile;
   __shared__ unsigned s_warp[SCAN_THREADS / 32];
   __shared__ unsigned s_prefix;
+  pdl_entry();
   if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u) - ticketBase;
   __syncthreads();
   const unsigned tile = s_tile;
@@ -130,6 +132,7 @@ __global__ void __launch_bounds__(256) k_scatter(DevParams d, const unsigned *__
                                                  const unsigned *__restrict__ cellStart, unsigned *__restrict__ cursor,
                                                  unsigned *__restrict__ tmpSerial,
                                                  const unsigned *__restrict__ rankKey, unsigned *__restrict__ tmpRankKey) {
+  pdl_entry();
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= d.N) return;
   unsigned cell = key[id];
@@ -154,8 +157,12 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
                                                       float *__restrict__ sortedType, float4 *__restrict__ spT, unsigned *__restrict__ cellList,
                                                       unsigned *__restrict__ cellListCount,
                                                       const unsigned *__restrict__ rankKey,
-                                                      float4 *__restrict__ recA, float4 *__restrict__ recB) {
+                                                      float4 *__restrict__ recA, float4 *__restrict__ recB,
+                                                      unsigned *__restrict__ cellCount) {
+  pdl_entry();
   int s = blockIdx.x * blockDim.x + threadIdx.x;
+  // the scatter cursors (the cell histogram, consumed by k_scatter) go back to zero for the next step's hash
+  for (int t = s; t <= d.G; t += gridDim.x * blockDim.x) cellCount[t] = 0u;
   if (s >= d.N) return;
   unsigned serial = tmpSerial[s];
   unsigned cell = key[serial];
@@ -224,33 +231,37 @@ static inline int blocks_for(int n, int t) { return (n + t - 1) / t; }
 
 void launch_hash_count(sph_ctx *c, bool write_pairs) {
   const int N = c->d.N;
-  cudaMemsetAsync(c->cellCount, 0, sizeof(unsigned) * ((size_t)c->d.G + 1), c->stream);
+  // k_rank_reorder leaves the histogram zeroed; only a histogram somebody else dirtied (a HASH stage without its SORT,
+  // a changed particle count) needs the memset — which would also break the chain of programmatic launches
+  if (!c->cellCountClean) cudaMemsetAsync(c->cellCount, 0, sizeof(unsigned) * ((size_t)c->d.G + 1), c->stream);
+  c->cellCountClean = false;
   if (write_pairs)
-    k_hash_count<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex,
-                                                                  c->scanState, c->scanTicket, c->scanTiles);
+    launch_k(c, k_hash_count<true>, dim3(blocks_for(N, 256)), dim3(256), c->d, c->position, c->key, c->cellCount,
+             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles);
   else
-    k_hash_count<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->position, c->key, c->cellCount, c->particleIndex,
-                                                                   c->scanState, c->scanTicket, c->scanTiles);
+    launch_k(c, k_hash_count<false>, dim3(blocks_for(N, 256)), dim3(256), c->d, c->position, c->key, c->cellCount,
+             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles);
 }
 
 void launch_sort(sph_ctx *c, bool fuse_reorder) {
   const int N = c->d.N, n = c->d.G + 1;
   // scan state and ticket were zeroed by k_hash_count: constant epoch, no per-step launch parameter
-  k_scan_cells<<<c->scanTiles, SCAN_THREADS, 0, c->stream>>>(c->cellCount, c->cellStart, n, c->scanState, c->scanTicket,
-                                                             0u, 1u, c->cellListCount);
-  k_scatter<<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->cellCount, c->tmpSerial, c->rankKey,
-                                                       c->tmpRankKey);
+  launch_k(c, k_scan_cells, dim3(c->scanTiles), dim3(SCAN_THREADS), c->cellCount, c->cellStart, n, c->scanState, c->scanTicket,
+           0u, 1u, c->cellListCount);
+  launch_k(c, k_scatter, dim3(blocks_for(N, 256)), dim3(256), c->d, c->key, c->cellStart, c->cellCount, c->tmpSerial, c->rankKey,
+           c->tmpRankKey);
   const unsigned *rk = c->rankKey ? c->tmpRankKey : nullptr;
+  // enough threads to zero the G + 1 histogram words too (sparse scenes have more cells than particles)
+  const int blocks = blocks_for(N, 256);
   if (fuse_reorder)
-    k_rank_reorder<true><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
-                                                                   c->particleIndex, c->particleIndexBack, c->position,
-                                                                   c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                   c->sortedType, c->spT, c->cellList, c->cellListCount, rk, c->recA, c->recB);
+    launch_k(c, k_rank_reorder<true>, dim3(blocks), dim3(256), c->d, c->key, c->cellStart, c->tmpSerial, c->particleIndex,
+             c->particleIndexBack, c->position, c->velocity, c->sortedPosition, c->sortedVelocity, c->sortedType, c->spT,
+             c->cellList, c->cellListCount, rk, c->recA, c->recB, c->cellCount);
   else
-    k_rank_reorder<false><<<blocks_for(N, 256), 256, 0, c->stream>>>(c->d, c->key, c->cellStart, c->tmpSerial,
-                                                                    c->particleIndex, c->particleIndexBack, c->position,
-                                                                    c->velocity, c->sortedPosition, c->sortedVelocity,
-                                                                    c->sortedType, c->spT, c->cellList, c->cellListCount, rk, c->recA, c->recB);
+    launch_k(c, k_rank_reorder<false>, dim3(blocks), dim3(256), c->d, c->key, c->cellStart, c->tmpSerial, c->particleIndex,
+             c->particleIndexBack, c->position, c->velocity, c->sortedPosition, c->sortedVelocity, c->sortedType, c->spT,
+             c->cellList, c->cellListCount, rk, c->recA, c->recB, c->cellCount);
+  c->cellCountClean = true;
 }
 
 void launch_reorder(sph_ctx *c) {

@@ -138,8 +138,8 @@ def test_configuration_loader_and_buffers_roundtrip(tmp_path):
     f0 = np.ctypeslib.as_array(pp, shape=(int(keep.sum()), 4)).copy()
     L.ow_helper_read_frame(C.byref(pp), C.byref(cc), C.byref(mm), 1)
     f1 = np.ctypeslib.as_array(pp, shape=(int(keep.sum()), 4)).copy()
-    # ostream << float prints 6 significant digits (as the reference): compare at that precision
-    assert np.allclose(f0, p2[keep], rtol=2e-6) and np.allclose(f1, p3[keep], rtol=2e-6)
+    # ostream << float prints 6 significant digits (as the reference): relative error up to 5e-6
+    assert np.allclose(f0, p2[keep], rtol=6e-6) and np.allclose(f1, p3[keep], rtol=6e-6)
     assert np.array_equal(np.ctypeslib.as_array(mm, shape=(2, 3)), mem)
 
 
@@ -298,7 +298,7 @@ def test_cli_driver_records_the_oracle_trajectory(tmp_path):
     want = np.concatenate([f[keep] for f in frames]).astype(np.float64)
     assert rows.shape == want.shape
     assert not np.isnan(want).any()
-    assert np.allclose(rows, want, rtol=2e-6, atol=0)
+    assert np.allclose(rows, want, rtol=6e-6, atol=0)
     # replay (-l_from) finds both frames
     r = subprocess.run([exe, "-l_from", "--buffers", str(tmp_path / "buffers")], capture_output=True, text=True, timeout=120, env=env)
     assert r.returncode == 0 and "replayed 2 frame(s)" in r.stdout, r.stdout

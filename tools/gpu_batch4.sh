@@ -1,0 +1,22 @@
+#!/bin/bash
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/b4_tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/b4_tests.log
+tail -8 gpurun_out/b4_tests.log
+python bench.py --steps 20 --warmup 3 > gpurun_out/b4_bench.json 2> gpurun_out/b4_bench.err; echo "bench rc=$?"
+tail -3 gpurun_out/b4_bench.err
+python - <<'P'
+import json
+for l in open('gpurun_out/b4_bench.json'):
+    if l.startswith('{'):
+        j=json.loads(l)
+        print('ms/step %.3f value %.4g e2e %.4g blocking %.4g launches %d'%(j['ms_per_step'],j['value'],j['e2e']['value'],j['e2e']['blocking_value'],j['gpu_launches']))
+        print({k:round(v*j['ms_per_step'],3) for k,v in j['roofline']['kernel_share_of_step'].items()})
+        for k,v in j.get('configs',{}).items(): print(k, {a:(round(b,4) if isinstance(b,float) else b) for a,b in v.items() if a in ('ms_per_step','value','e2e_value','e2e_blocking_value','x_cpu','x_cpu_e2e','cpu_value')})
+P
+for wl in config_a config_b; do python bench.py --workload $wl --steps 200 --warmup 10 --no-cpu-baseline --no-configs 2>&1 | python -c "
+import sys,json
+for l in sys.stdin:
+    if l.startswith('{'):
+        j=json.loads(l); print('$wl ms/step %.4f'%j['ms_per_step']); print({k:round(v*j['ms_per_step'],4) for k,v in j['roofline']['kernel_share_of_step'].items()})
+"; done
+bash tools/sanitize.sh
