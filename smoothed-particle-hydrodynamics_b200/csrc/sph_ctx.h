@@ -79,9 +79,9 @@ struct sph_ctx {
   int graphNodes[2];           // kernels in each captured half
   int graph_mode;              // -1 = by size, 0 = never, 1 = always
   bool capturing;              // inside stream capture: launchers must not touch events of other streams
-  int pdl_mode;                // SPH_PDL: -1 = with the graph, 0 = never, 1 = always
+  int pdl_mode;                // SPH_PDL: 1 = on, otherwise off (measured: no gain over the graph replay)
   bool graphPdl;               // the captured graphs were recorded with programmatic launches
-  bool pdl;                    // programmatic dependent launch between the kernels of the step (SPH_PDL=0|1, default: with the graph)
+  bool pdl;                    // programmatic dependent launch between the kernels of the step (SPH_PDL=1; default off)
   bool cellCountClean;         // the cell histogram is all zero (k_rank_reorder left it so): no memset before the next hash
   int lanes;                   // SPH_LANES: lanes per particle of the small-scene gather kernels (0 = by size)
   // pipelined read-back (sph_read_begin / sph_read_end): a device-to-host copy of position or velocity that

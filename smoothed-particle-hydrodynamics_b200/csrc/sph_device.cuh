@@ -48,13 +48,15 @@ struct DevParams {
   float d2H, d2Close;
 };
 
-// Programmatic dependent launch (sm_90+): first statement of every kernel of the fused step. launch_dependents lets
-// the NEXT kernel of the stream be scheduled as soon as all CTAs of this one are resident, so its launch latency and
-// ramp-up overlap this kernel's tail; wait blocks until the PREVIOUS kernel has completed and its writes are visible
-// (transitively: it passed its own wait). Both are no-ops for launches without the programmatic attribute.
+// Programmatic dependent launch (sm_90+): first statement of every kernel of the fused step. wait blocks until the
+// PREVIOUS kernel of the stream has completed and its writes are visible; launch_dependents then lets the NEXT kernel
+// be scheduled as soon as all CTAs of this one have got here, so its launch latency and ramp-up overlap this kernel's
+// execution. Wait comes FIRST: at most two grids of the chain are then in flight. (Triggering before waiting let a
+// third grid start while the first still ran, and its wait did not cover the first: measured as stale reads in the
+// worm scene, tools/diag_worm.py.) Both are no-ops for launches without the programmatic attribute.
 __device__ __forceinline__ void pdl_entry() {
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
 // ---- float4 lane-wise helpers (OpenCL vector semantics, one IEEE op per lane) ----

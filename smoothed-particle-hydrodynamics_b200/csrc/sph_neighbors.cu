@@ -202,6 +202,9 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #ifndef LP_EOVF
 #define LP_EOVF 28
 #endif
+#ifndef LP_HIST_FIRST_N
+#define LP_HIST_FIRST_N 40   // filter hits (without the particle itself) from which the histogram is built in the first pass
+#endif
 
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
 // 256-bit loads of a sweep pass share one address computation.
@@ -492,17 +495,20 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
       hist3 += (w == 3) ? inc : 0ull;
     }
   };
-  // VAR 2 only COUNTS the candidates within h in the first pass: with fewer than 32 of them the running sum of the
-  // radial histogram never reaches 32 and r_thr keeps its largest value whatever the bins are (sphFluid.cl:310-324),
-  // so the histogram is built (in a pass of its own) only for the particles that have 32 or more — none or few in a
-  // fluid near rest density, all in a compressed one.
+  // VAR 2 only COUNTS the candidates within h in the first pass when the particle has few filter hits: with fewer
+  // than 32 within h the running sum of the radial histogram never reaches 32 and r_thr keeps its largest value
+  // whatever the bins are (sphFluid.cl:310-324), so the histogram is built (in a pass of its own) only if the count
+  // reaches 32 after all — rare in a fluid near rest density (fluid_8m: 2.93 -> 2.74 ms). A particle with many hits
+  // (dense or compressed matter: the worm's elastic body, a settled pool) will need it: it builds it in the first pass.
+  const bool histFirst = VAR != 2 || n - 1 >= LP_HIST_FIRST_N;
   int within = 0;
   auto first_pass = [&](unsigned hv) {
     const int j = hit_index(hv);
     if (j == id) return;
     const float dd = dist2(j);
     if (dd <= h2) {
-      if (VAR == 2) within++; else hist_add(dd);
+      within++;
+      if (histFirst) hist_add(dd);
     }
     if (dd <= r2open && found < SPH_NB) take(j, dd);
   };
@@ -523,7 +529,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   };
   if (VAR == 2) {
     for (int t = 0; t < n; t++) first_pass(next_hit());
-    if (within >= SPH_NB) {   // the histogram decides r_thr: build it
+    if (!histFirst && within >= SPH_NB) {   // the histogram decides r_thr after all: build it
       curMask = 0u;
       curEntry = 0;
       for (int t = 0; t < n; t++) {
