@@ -280,6 +280,21 @@ void *sph_device_alloc(size_t bytes);
 void sph_device_free(void *p);
 int sph_device_copy(void *dst, const void *src, size_t bytes);
 
+/* ---- allocation-free entry point. NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * sph_cell_start_noalloc computes gridCellIndexFixedUp — for every hash cell the number of particles in cells with a
+ * smaller id, i.e. what SPH_STAGE_HASH_PARTICLES + SPH_STAGE_SORT leave in SPH_BUF_GRID_CELL_INDEX_FIXED_UP — from
+ * DEVICE positions into a DEVICE output, asynchronously on `cuda_stream` (NULL = the default stream) of the CURRENT
+ * device. It allocates nothing: the cell histogram lives in a static device array of SPH_NOALLOC_MAX_CELLS words
+ * (4 MiB held by every GPU that loads the library, until exit); grid_cell_count + 1 beyond that is rejected with
+ * SPH_E_SIZE. All calls share the array: it is cleared at the start of each call, and calls that overlap on the
+ * GPU (different streams) race. pos4_device: n float4 (x, y, z, type); cell_start_device: grid_cell_count + 1 uint32. */
+#define SPH_NOALLOC_MAX_CELLS (1 << 20)
+int sph_cell_start_noalloc(const sph_params *p, const float *pos4_device, int n, uint32_t *cell_start_device,
+                           void *cuda_stream);
+int sph_noalloc_max_cells(void);
+const char *sph_noalloc_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

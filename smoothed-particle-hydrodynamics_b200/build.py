@@ -15,7 +15,7 @@ CSRC = os.path.join(PKG, "csrc")
 INC = os.path.join(PKG, "..", "include")
 LIB = os.path.join(PKG, "libsph_b200.so")
 OBJ = os.path.join(PKG, "build")
-SOURCES = ["sph_sort.cu", "sph_neighbors.cu", "sph_pcisph.cu", "sph_lanes.cu", "sph_membranes.cu", "sph_slab.cu", "sph_capi.cu"]
+SOURCES = ["sph_sort.cu", "sph_neighbors.cu", "sph_pcisph.cu", "sph_lanes.cu", "sph_membranes.cu", "sph_slab.cu", "sph_noalloc.cu", "sph_capi.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
