@@ -26,6 +26,12 @@ extern float *muscle_activation_signal_cpp;
 void owSetBox(double xmax_in_h, double ymax_in_h, double zmax_in_h);
 void owSetHashMask(unsigned int mask);
 void owSetDevice(int cuda_ordinal);
+// Addition (the reference is single-device, owOpenCLSolver.cpp:157-182): run ONE fluid on several GPUs of this process.
+// The solver cuts the hash grid into z-slabs (one per entry of `cuda_ordinals`; an ordinal may repeat), links the
+// slabs through peer memory (sph_slab_link_local) and steps them with sph_slab_step_begin / _end; read_position_buffer
+// assembles the global array in the caller's particle order. Needs owSetHashMask(0xffffffff) and a scene without elastic
+// matter; results are bit-identical to the single-device run. n <= 1 restores the single-device solver.
+void owSetSlabDevices(const int *cuda_ordinals, int n);
 // Fill *p from the globals above + the current box (what every solver is created with).
 void owCurrentParams(sph_params *p);
 
@@ -69,11 +75,18 @@ class owOpenCLSolver {
   void snapshot(bool with_velocity); // freeze rho / particleIndex (/ velocity) of the step queued so far for the read_* methods
   void setReadFromSnapshot(bool on) { fromSnapshot = on; }
   sph_ctx *context() { return ctx; }
+  int slabCount() const { return numSlabs; }
 
  private:
   unsigned int stage(int id);
+  void createSlabs(const float *position_cpp, const float *velocity_cpp);
+  void destroySlabs();
   sph_ctx *ctx;
   bool fromSnapshot;
+  // several devices (owSetSlabDevices): one context per slab, host staging for the read-back
+  struct Slab { sph_ctx *ctx; float *pos; unsigned int *gid; int capacity; };
+  Slab *slabs;
+  int numSlabs;
 };
 
 #endif  // OW_OPENCL_SOLVER_H

@@ -194,6 +194,8 @@ int sph_run_steps(sph_ctx *ctx, int steps, float *elapsed_ms);
 /* Device timer (CUDA events on the context's stream, synchronize on both sides) around work the caller queues itself. */
 int sph_timer_start(sph_ctx *ctx);
 int sph_timer_stop(sph_ctx *ctx, float *elapsed_ms);
+/* Cost of a dependent chain of `nodes` EMPTY kernels replayed as a CUDA graph (the floor of a launch-bound step). */
+int sph_empty_chain_ms(sph_ctx *ctx, int nodes, int blocks, int threads, int replays, float *ms_per_replay);
 /* Per-kernel CUDA-event timing of sph_step on/off; report = JSON {"kernel": {"calls":n,"ms":t}}. */
 int sph_profile_enable(sph_ctx *ctx, int on);
 int sph_profile_report(sph_ctx *ctx, char *buf, size_t n);

@@ -114,6 +114,7 @@ class SphLib:
             L.sph_host_free.argtypes = [C.c_void_p]
             L.sph_host_free.restype = None
             L.sph_timer_start.argtypes = [C.c_void_p]
+            L.sph_empty_chain_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, P(C.c_float)]
             L.sph_timer_stop.argtypes = [C.c_void_p, P(C.c_float)]
 
     @property
@@ -214,6 +215,11 @@ class SphContext:
     def stream_timer_stop(self, _token=None):
         ms = C.c_float(0)
         self.L.check(self.L.lib.sph_timer_stop(self.h, C.byref(ms)), "sph_timer_stop")
+        return float(ms.value)
+
+    def empty_chain_ms(self, nodes, blocks=240, threads=256, replays=200):
+        ms = C.c_float(0)
+        self.L.check(self.L.lib.sph_empty_chain_ms(self.h, int(nodes), int(blocks), int(threads), int(replays), C.byref(ms)), "sph_empty_chain_ms")
         return float(ms.value)
 
     def profile(self, on):

@@ -187,7 +187,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soa, c->tmpRankKey, c->memList, c->memCount};
+                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soa, c->tmpRankKey, c->memList, c->memCount, c->nsStats};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -302,6 +302,7 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->fnDeferred, N));
   A(dalloc(&c->scanState, (size_t)c->scanTiles));
   A(dalloc(&c->scanTicket, 1));
+  A(dalloc(&c->nsStats, 2));
   if (ok) A(cudaMemcpy(c->position, pos4, 16 * N, cudaMemcpyHostToDevice));   // owOpenCLSolver.cpp:65
   if (ok) A(cudaMemcpy(c->velocity, vel4, 16 * N, cudaMemcpyHostToDevice));   // :66
   if (ok && c->has_membranes) {                                                // :70-71
@@ -641,6 +642,35 @@ int sph_run_steps(sph_ctx *c, int steps, float *elapsed_ms) {
   cudaEventDestroy(a);
   cudaEventDestroy(b);
   if (elapsed_ms) *elapsed_ms = ms;
+  return 0;
+}
+
+// Floor of a launch-bound step: a captured graph of `nodes` dependent EMPTY kernels (blocks x threads each), replayed
+// `replays` times on the context's stream; *ms_per_replay is what the dependent-launch chain alone costs on this GPU.
+// bench.py prints it beside the small-scene step times (why 61 k particles cannot go below ~N x this).
+int sph_timer_start(sph_ctx *c);
+int sph_timer_stop(sph_ctx *c, float *elapsed_ms);
+__global__ void k_empty_node(int *sink) { if (sink && threadIdx.x == 0xffff) *sink = 0; }
+int sph_empty_chain_ms(sph_ctx *c, int nodes, int blocks, int threads, int replays, float *ms_per_replay) {
+  if (!c || nodes < 1 || blocks < 1 || threads < 1 || threads > 1024 || replays < 1 || !ms_per_replay) return fail(SPH_E_INVALID, "sph_empty_chain_ms");
+  CU(cudaSetDevice(c->device));
+  cudaGraph_t g = nullptr;
+  cudaGraphExec_t ge = nullptr;
+  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+  for (int i = 0; i < nodes; i++) k_empty_node<<<blocks, threads, 0, c->stream>>>(nullptr);
+  CU(cudaStreamEndCapture(c->stream, &g));
+  CU(cudaGraphInstantiate(&ge, g, 0));
+  cudaGraphDestroy(g);
+  for (int i = 0; i < 3; i++) CU(cudaGraphLaunch(ge, c->stream));
+  int rc = sph_timer_start(c);
+  if (rc) return rc;
+  for (int i = 0; i < replays; i++) CU(cudaGraphLaunch(ge, c->stream));
+  float ms = 0.f;
+  rc = sph_timer_stop(c, &ms);
+  cudaGraphExecDestroy(ge);
+  if (rc) return rc;
+  *ms_per_replay = ms / replays;
   return 0;
 }
 

@@ -202,9 +202,7 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #ifndef LP_EOVF
 #define LP_EOVF 28
 #endif
-#ifndef LP_HIST_FIRST_N
-#define LP_HIST_FIRST_N 40   // filter hits (without the particle itself) from which the histogram is built in the first pass
-#endif
+
 
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
 // 256-bit loads of a sweep pass share one address computation.
@@ -256,7 +254,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
                                                                     const float *__restrict__ S,
                                                                     const unsigned *__restrict__ cellStart,
                                                                     int *__restrict__ nb, float *__restrict__ rho,
-                                                                    float4 *__restrict__ recA) {
+                                                                    float4 *__restrict__ recA, unsigned *nsStats) {
   __shared__ unsigned short hits[VAR == 2 ? 1 : LP_CAP + 1][LP_THREADS];
   __shared__ unsigned ent[VAR == 2 ? LP_ECAP + 1 : 1][LP_THREADS];
   __shared__ int binCount[64], binBase[64];
@@ -495,12 +493,13 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
       hist3 += (w == 3) ? inc : 0ull;
     }
   };
-  // VAR 2 only COUNTS the candidates within h in the first pass when the particle has few filter hits: with fewer
-  // than 32 within h the running sum of the radial histogram never reaches 32 and r_thr keeps its largest value
-  // whatever the bins are (sphFluid.cl:310-324), so the histogram is built (in a pass of its own) only if the count
-  // reaches 32 after all — rare in a fluid near rest density (fluid_8m: 2.93 -> 2.74 ms). A particle with many hits
-  // (dense or compressed matter: the worm's elastic body, a settled pool) will need it: it builds it in the first pass.
-  const bool histFirst = VAR != 2 || n - 1 >= LP_HIST_FIRST_N;
+  // VAR 2 can leave the radial histogram out of the first pass: with fewer than 32 candidates within h its running sum
+  // never reaches 32 and r_thr keeps its largest value whatever the bins are (sphFluid.cl:310-324); a particle that
+  // turns out to have 32 or more builds it in a pass of its own. That pays in a fluid near rest density (fluid_8m:
+  // 2.93 -> 2.74 ms) and costs in dense matter, where most particles need the extra pass (worm scene 0.141 -> 0.155 ms).
+  // The choice is made per STEP for all threads alike (a per-thread choice diverges inside the warps and costs both):
+  // nsStats[1], set by k_hash_count from the number of particles that needed the histogram in the previous step.
+  const bool histFirst = VAR != 2 || nsStats == nullptr || nsStats[1] != 0u;
   int within = 0;
   auto first_pass = [&](unsigned hv) {
     const int j = hit_index(hv);
@@ -575,6 +574,11 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     density *= d.massWpoly6;
     rho[id] = (float)density;
     if (recA) reinterpret_cast<float *>(recA)[8 * (size_t)id + 7] = (float)density;
+  }
+  if (VAR == 2 && nsStats) {  // statistic for the next step's choice: one atomic per warp
+    const unsigned act = __activemask();
+    const unsigned m = __ballot_sync(act, within >= SPH_NB);
+    if ((threadIdx.x & 31) == __ffs(act) - 1 && m) atomicAdd(&nsStats[0], (unsigned)__popc(m));
   }
 }
 
@@ -1367,7 +1371,7 @@ void launch_find_neighbors(sph_ctx *c, bool with_density) {
     const int blocks = (n + LP_THREADS - 1) / LP_THREADS;
 #define LP_LAUNCH(WD, V, REC)                                                                                      \
   launch_k(c, k_find_neighbors_list<WD, V>, dim3(blocks), dim3(LP_THREADS), c->d, c->sortedPosition, c->soa, c->cellStart, \
-           c->nbIds, c->rho, (float4 *)(REC))
+           c->nbIds, c->rho, (float4 *)(REC), c->nsStats)
     if (var == 0) { if (with_density) LP_LAUNCH(true, 0, c->recA); else LP_LAUNCH(false, 0, nullptr); }
     else if (var == 1) { if (with_density) LP_LAUNCH(true, 1, c->recA); else LP_LAUNCH(false, 1, nullptr); }
     else { if (with_density) LP_LAUNCH(true, 2, c->recA); else LP_LAUNCH(false, 2, nullptr); }

@@ -26,9 +26,13 @@ __global__ void __launch_bounds__(256) k_hash_count(DevParams d, const float4 *_
                                                     unsigned *__restrict__ key, unsigned *__restrict__ cellCount,
                                                     uint2 *__restrict__ particleIndex,
                                                     unsigned long long *__restrict__ scanState,
-                                                    unsigned *__restrict__ scanTicket, int scanTiles) {
+                                                    unsigned *__restrict__ scanTicket, int scanTiles,
+                                                    unsigned *__restrict__ nsStats) {
   pdl_entry();
   int id = blockIdx.x * blockDim.x + threadIdx.x;
+  // neighbour search of this step: histogram in the first pass if more than a quarter of the particles needed it in
+  // the previous step (see k_find_neighbors_list); then restart the count
+  if (id == 0) { nsStats[1] = (4ull * nsStats[0] > (unsigned long long)d.N) ? 1u : 0u; nsStats[0] = 0u; }
   // reset the look-back scan of this step's sort (k_scan_cells runs after this kernel): the step's launch
   // parameters are then the same every step, which is what lets sph_step replay a captured CUDA graph
   for (int t = id; t < scanTiles; t += gridDim.x * blockDim.x) scanState[t] = 0ull;
@@ -237,10 +241,10 @@ void launch_hash_count(sph_ctx *c, bool write_pairs) {
   c->cellCountClean = false;
   if (write_pairs)
     launch_k(c, k_hash_count<true>, dim3(blocks_for(N, 256)), dim3(256), c->d, c->position, c->key, c->cellCount,
-             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles);
+             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles, c->nsStats);
   else
     launch_k(c, k_hash_count<false>, dim3(blocks_for(N, 256)), dim3(256), c->d, c->position, c->key, c->cellCount,
-             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles);
+             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles, c->nsStats);
 }
 
 void launch_sort(sph_ctx *c, bool fuse_reorder) {

@@ -4,12 +4,13 @@
 //   -l_to            record buffers/*.txt on step 0 and every 10th step
 //   -l_from          replay buffers/position_buffer.txt frame by frame (no physics), print frame count
 // additions: --steps N (default 100), --box X Y Z (multiples of h; default header box 30 20 250),
-//   --config DIR [--position F --velocity F], --buffers DIR, --mask HEX, --staged, --quiet, --device N
+//   --config DIR [--position F --velocity F], --buffers DIR, --mask HEX, --staged, --quiet, --device N, --devices a,b,.. (one z-slab per listed GPU; needs --mask ffffffff)
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
 #include <iostream>
+#include <vector>
 
 #include "ow/owPhysicsFluidSimulator.h"
 
@@ -29,6 +30,11 @@ int main(int argc, char **argv) {
     else if (!strcmp(argv[i], "--buffers") && i + 1 < argc) owHelper::setBuffersDir(argv[++i]);
     else if (!strcmp(argv[i], "--mask") && i + 1 < argc) owSetHashMask((unsigned)strtoul(argv[++i], 0, 16));
     else if (!strcmp(argv[i], "--device") && i + 1 < argc) owSetDevice(atoi(argv[++i]));
+    else if (!strcmp(argv[i], "--devices") && i + 1 < argc) {  // "0,1,2,3": one z-slab of the fluid per listed GPU
+      std::vector<int> dv;
+      for (char *t = strtok(argv[++i], ","); t; t = strtok(0, ",")) dv.push_back(atoi(t));
+      owSetSlabDevices(dv.data(), (int)dv.size());
+    }
     else if (!strcmp(argv[i], "--staged")) staged = true;
     else if (!strcmp(argv[i], "--quiet")) owHelper::quiet = true;
     else { fprintf(stderr, "unknown argument %s\n", argv[i]); return 2; }

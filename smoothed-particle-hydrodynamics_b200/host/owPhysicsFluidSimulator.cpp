@@ -133,11 +133,11 @@ double owPhysicsFluidSimulator::simulationStep(const bool load_to) {
   helper->refreshTime();
   if (!owHelper::quiet) printf("\n[[ Step %d ]]\n", iterationCount);
   try {
-    if (fused || stepInFlight) {
+    if (fused || stepInFlight || ocl_solver->slabCount() > 0) {
       // same results as the 18 stages below, as one asynchronous launch sequence
       if (!stepInFlight && ocl_solver->_runFusedStep()) throw std::runtime_error(sph_last_error());
       stepInFlight = false;
-      if (fused && runAhead) {
+      if (fused && runAhead && ocl_solver->slabCount() == 0) {
         // Run ahead: step k is queued (or running). Freeze what the getters of step k read, start the position
         // read-back on the copy stream, produce the inputs of step k+1 — the muscle signal, which the reference
         // also updates at the end of the step, before the next one starts (:131-139) — and queue step k+1, whose

@@ -9,6 +9,7 @@ extern "C" {
 void ow_set_box(double x, double y, double z) { owSetBox(x, y, z); }
 void ow_set_hash_mask(unsigned int m) { owSetHashMask(m); }
 void ow_set_device(int d) { owSetDevice(d); }
+void ow_set_slab_devices(const int *ordinals, int n) { owSetSlabDevices(ordinals, n); }
 void ow_set_quiet(int q) { owHelper::quiet = q != 0; }
 void ow_set_configuration_files(const char *dir, const char *pos, const char *vel) { owHelper::setConfigurationFiles(dir, pos, vel); }
 void ow_set_buffers_dir(const char *dir) { owHelper::setBuffersDir(dir); }

@@ -302,3 +302,42 @@ def test_cli_driver_records_the_oracle_trajectory(tmp_path):
     # replay (-l_from) finds both frames
     r = subprocess.run([exe, "-l_from", "--buffers", str(tmp_path / "buffers")], capture_output=True, text=True, timeout=120, env=env)
     assert r.returncode == 0 and "replayed 2 frame(s)" in r.stdout, r.stdout
+
+
+@pytest.mark.gpu
+def test_simulator_on_several_slabs_matches_single_device():
+    """The drop-in class with owSetSlabDevices (the reference is single-device): one fluid cut into z-slabs inside one
+    process, linked through peer memory, global position array assembled by read_position_buffer. Two slabs on GPU 0
+    here (one GPU is enough: an ordinal may repeat); per particle the positions and velocities of the single-device
+    oracle run, bit for bit, while particles migrate between the slabs."""
+    L = host_lib()
+    L.ow_set_slab_devices.argtypes = [C.POINTER(C.c_int), C.c_int]
+    L.ow_set_hash_mask.argtypes = [C.c_uint]
+    O = common.oracle_lib()
+    pos, vel = common.synthetic_block(14, 12, 40, (24, 22, 96), seed=7)
+    liquid = pos[:, 3] < 2
+    rng = np.random.RandomState(7)
+    vel[liquid, 2] = (0.45 + 0.1 * rng.rand(int(liquid.sum()))).astype(np.float32)   # thrown along z: layers change slab
+    p = common.fill_counts(O.default_params(box=(12, 11, 48)), pos)
+    p.hash_mask = 0xFFFFFFFF
+    o = O.create(p, pos, vel)
+    L.ow_set_box(12.0, 11.0, 48.0)
+    L.ow_set_hash_mask(0xFFFFFFFF)
+    devs = (C.c_int * 2)(0, 0)
+    L.ow_set_slab_devices(devs, 2)
+    try:
+        sim = L.ow_sim_create(len(pos), vp(pos), vp(vel), 0, None, 0, None, None)
+        L.ow_sim_set_muscle_hook(sim, 0)
+        for s in range(8):
+            L.ow_sim_step(sim, 0)
+            o.step()
+            got = np.ctypeslib.as_array(L.ow_sim_position(sim), shape=(len(pos), 4))
+            assert common.first_mismatch(got, o.read("position", len(pos))) is None, "step %d" % s
+        v = np.zeros((len(pos), 4), np.float32)
+        L.ow_sim_read_velocity(sim, vp(v))
+        assert common.first_mismatch(v, o.read("velocity", len(pos))) is None
+        L.ow_sim_destroy(sim)
+    finally:
+        L.ow_set_slab_devices(devs, 0)
+        L.ow_set_hash_mask(0xFFFF)
+    o.close()
