@@ -341,3 +341,72 @@ def test_simulator_on_several_slabs_matches_single_device():
         L.ow_set_slab_devices(devs, 0)
         L.ow_set_hash_mask(0xFFFF)
     o.close()
+
+
+# ---------------------------------------------------------------- config B': the shipped position.txt with regenerated springs
+def _bprime():
+    sys.path.insert(0, os.path.join(common.ROOT, "tools"))
+    import make_connections
+    z = np.load(os.path.join(common.GOLDEN, "configBprime.npz"))   # /root/reference/configuration/position.txt + velocity.txt
+    pos, vel = z["position"], z["velocity"]
+    return pos, vel, make_connections.connections(pos), make_connections
+
+
+def test_regenerated_connections_follow_the_generator_rule():
+    """elasticconnections.txt of the shipped position.txt is a lost blob; tools/make_connections.py rebuilds it with
+    the generator's spring rule (owHelper.cpp:972-1001). Properties of that rule: springs only from elastic particles,
+    never to liquid ones, candidates in index order, r_ij <= r0*sqrt(2.7), rest length 0.95 r_ij (scaled), elastic-elastic
+    springs symmetric."""
+    pos, vel, con, mc = _bprime()
+    t = pos[:, 3].astype(int)
+    el = np.nonzero(t == 2)[0]
+    assert con.shape == (32 * len(el), 4) and len(el) == 7327
+    rows = con.reshape(len(el), 32, 4)
+    jd = rows[:, :, 0]
+    used = jd >= 0
+    assert used.sum() > 100000 and used.sum(1).max() <= 32
+    assert (np.diff(used.astype(int), axis=1) <= 0).all()            # filled from slot 0, no holes
+    j = jd[used].astype(int)
+    i = np.repeat(el, 32).reshape(len(el), 32)[used]
+    assert (t[j] != 1).all() and (j != i).all()
+    d = np.linalg.norm(pos[i, :3].astype(np.float64) - pos[j, :3].astype(np.float64), axis=1)
+    assert (d <= 0.5 * 3.34 * np.sqrt(2.7) * (1 + 1e-6)).all()
+    assert np.allclose(rows[:, :, 1][used], d * float(mc.simulation_scale()) * 0.95, rtol=1e-5)
+    jsorted = np.where(used, jd, np.inf)
+    assert (np.diff(jsorted, axis=1)[used[:, 1:]] > 0).all()         # index order
+    pairs = set(zip(i.tolist(), j.tolist()))
+    assert all((b, a) in pairs for a, b in pairs if t[b] == 2)
+
+
+@pytest.mark.gpu
+def test_simulator_config_bprime_from_files(tmp_path):
+    """Config B' end to end through the drop-in class: configuration/position.txt, velocity.txt and the regenerated
+    elasticconnections.txt are read by owHelper (boundary particles first: elastic offset = numOfBoundaryP,
+    owOpenCLSolver.cpp:435), stepped on the GPU, compared with the oracle bit for bit."""
+    L = host_lib()
+    O = common.oracle_lib()
+    pos, vel, con, mc = _bprime()
+    d = tmp_path / "configuration"
+    d.mkdir()
+    write_txt(d / "position.txt", pos)
+    write_txt(d / "velocity.txt", vel)
+    mc.write_txt(d / "elasticconnections.txt", con)
+    L.ow_set_configuration_files(str(d).encode(), b"position.txt", b"velocity.txt")
+    L.ow_set_box(36.0, 24.0, 54.5)
+    sim = L.ow_sim_create_from_files()
+    L.ow_sim_set_muscle_hook(sim, 0)
+    p = common.fill_counts(O.default_params(box=(36, 24, 54.5)), pos)
+    p.elastic_offset = p.num_boundary
+    o = O.create(p, pos, vel, elastic=con)
+    for s in range(4):
+        L.ow_sim_step(sim, 0)
+        o.step()
+        got = np.ctypeslib.as_array(L.ow_sim_position(sim), shape=(len(pos), 4))
+        want = o.read("position", len(pos))
+        assert not np.isnan(want).any()
+        assert common.first_mismatch(got, want) is None, "step %d" % s
+    v = np.zeros((len(pos), 4), np.float32)
+    L.ow_sim_read_velocity(sim, vp(v))
+    assert common.first_mismatch(v, o.read("velocity", len(pos))) is None
+    L.ow_sim_destroy(sim)
+    o.close()
