@@ -56,6 +56,31 @@ def build(force=False, verbose=False, ptxas_info=False):
     return LIB
 
 
+def build_variant(name, defines, verbose=False):
+    """Experiment builds: the library with extra -D macros -> build_exp/libsph_<name>.so (git-ignored; selected at run
+    time with SPH_LIB=<path>, see capi.load_product). Not part of the product build."""
+    out_dir = os.path.join(PKG, "build_exp")
+    os.makedirs(out_dir, exist_ok=True)
+    objs = []
+    def run(cmd):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("nvcc failed: " + " ".join(cmd))
+    cmds = []
+    for s in SOURCES:
+        obj = os.path.join(out_dir, name + "_" + s.replace(".cu", ".o"))
+        objs.append(obj)
+        cmds.append([NVCC] + FLAGS + ["-D" + d for d in defines] + ["-c", os.path.join(CSRC, s), "-o", obj])
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        list(ex.map(run, cmds))
+    lib = os.path.join(out_dir, "libsph_%s.so" % name)
+    run([NVCC, "-shared", "-o", lib] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart_static", "-ldl", "-lrt", "-lpthread"])
+    for o in objs:
+        os.remove(o)
+    return lib
+
+
 HOST = os.path.join(PKG, "host")
 HOST_LIB = os.path.join(PKG, "libow_b200.so")
 HOST_BIN = os.path.join(PKG, "sibernetic_b200")

@@ -275,6 +275,9 @@ PRODUCT_LIB = os.path.join(_PKG, "libsph_b200.so")
 
 def load_product():
     """The CUDA library. Fails loudly if it has not been built — there is no CPU fallback."""
+    exp = os.environ.get("SPH_LIB")   # experiment builds (build.build_variant); never set in the product
+    if exp:
+        return SphLib(exp)
     if not os.path.exists(PRODUCT_LIB):
         raise SphError("CUDA library %s is missing: run `python -c 'import __graft_entry__ as g; g.build()'`" % PRODUCT_LIB)
     return SphLib(PRODUCT_LIB)

@@ -187,7 +187,7 @@ void sph_destroy(sph_ctx *c) {
   void *ptrs[] = {c->position, c->velocity, c->particleIndex, c->particleIndexBack, c->sortedPosition,
                   c->sortedVelocity, c->gridCellIndex, c->cellStart, c->rho, c->pressure, c->acceleration,
                   c->elastic, c->membraneData, c->pml, c->muscle, c->nbIds, c->cellCount, c->key, c->tmpSerial,
-                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soa, c->tmpRankKey, c->memList, c->memCount, c->nsStats};
+                  c->sortedType, c->spT, c->recA, c->recB, c->cellList, c->cellListCount, c->cellCursor, c->fnDeferred, c->scanState, c->scanTicket, c->nmScratch, c->readScratch, c->elasticMask, c->soa, c->tmpRankKey, c->memList, c->memCount, c->nsStats, c->bMask};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   if (c->profiler) sph_profile_enable(c, 0);
@@ -267,6 +267,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
     c->graph_mode = gm ? atoi(gm) : -1;
     const char *ln = getenv("SPH_LANES");
     c->lanes = ln ? atoi(ln) : 0;
+    const char *hp = getenv("SPH_HIST_PCT");
+    c->hist_pct = hp ? (unsigned)atoi(hp) : 5u;
     const char *pd = getenv("SPH_PDL");
     c->pdl_mode = pd ? atoi(pd) : -1;
   }
@@ -295,7 +297,8 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->sortedType, N));
   A(dalloc(&c->spT, N));
   A(dalloc(&c->recA, 2 * N));
-  A(dalloc(&c->recB, 2 * N));
+  A(dalloc(&c->recB, N));
+  A(dalloc(&c->bMask, N));
   A(dalloc(&c->cellList, (G < N ? G : N) + 1));
   A(dalloc(&c->cellListCount, 1));
   A(dalloc(&c->cellCursor, 2));

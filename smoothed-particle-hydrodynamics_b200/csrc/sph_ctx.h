@@ -33,7 +33,8 @@ struct sph_ctx {
   unsigned *tmpSerial;         // N counting-sort scatter target
   float *sortedType;           // N type tag (position.w) in sorted order
   float4 *spT;                 // N sorted (x, y, z, type tag): the copy the force kernels gather
-  float4 *recA, *recB;         // 2N each: 32-byte gather records of the fused path (see ld256, sph_device.cuh)
+  float4 *recA, *recB;         // gather records of the fused path (sph_device.cuh): recA 2N (32 bytes per particle), recB N (16 bytes)
+  unsigned *bMask;             // N words: bit k = neighbour slot k holds a boundary particle (written by the forces kernel)
   unsigned *cellList;          // first non-empty cell of every home block (cell pair) of this step (order arbitrary)
   unsigned *cellListCount;
   unsigned *cellCursor;        // [0] work cursor of the tiled neighbour search, [1] length of fnDeferred
@@ -62,6 +63,7 @@ struct sph_ctx {
   float2 *nmScratch;           // 32N float2, lazily allocated for sph_read(NEIGHBOR_MAP)
   float4 *readScratch;
   unsigned *elasticMask;       // N words, scenes with membranes only: bit k = neighbour slot k holds an elastic particle
+  unsigned hist_pct;           // SPH_HIST_PCT (see k_hash_count)
   unsigned *nsStats;           // [0] particles that needed the radial histogram this step, [1] this step's mode (k_hash_count)
   int *memList, *memCount;     // scenes with membranes: sorted ids of the liquid particles with an elastic neighbour (this step)
   bool has_elastic, has_membranes, has_pml;

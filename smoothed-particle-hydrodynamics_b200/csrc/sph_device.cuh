@@ -75,7 +75,12 @@ __device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
 // Gather RECORDS of the fused path: one 32-byte, 32-byte-aligned record per sorted particle, fetched with a
 // single 256-bit load (LDG.E.256, one L1/L2 sector) instead of two or three 16-byte gathers from separate arrays.
 //   recA[i] = (x, y, z, type | vx, vy, vz, rho(t))   gathered by the viscosity / surface-tension kernel
-//   recB[i] = (x, y, z, type | p, rho*, 0, 0)        gathered by the pressure-force kernel
+//   recB[i] = (x, y, z, p)  — 16 bytes, ONE 128-bit gather — for the pressure-force kernel: positions at time t and
+//             the current pressure. rho*_j lives in rho[N + j] and is fetched only for the pairs that carry pressure
+//             (most pairs of a fluid near rest do not, see pressure_term); the neighbour's TYPE, which round 1 kept in
+//             this record for the integration's boundary handling, is now a bit mask per particle (bMask / elasticMask)
+//             that the forces kernel derives from recA once per step. A 16-byte gather costs ~12 L1 wavefronts per warp
+//             request against ~22 for a 32-byte one, and the kernel is bound by exactly that (L1 data pipe 98 %).
 __device__ __forceinline__ void ld256(const float4 *rec, float4 &a, float4 &b) {
   asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)

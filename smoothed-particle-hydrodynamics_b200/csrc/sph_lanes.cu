@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
                                                              const int *__restrict__ nb, const float *__restrict__ rho,
                                                              float4 *__restrict__ acc, float *__restrict__ pressure,
                                                              float4 *__restrict__ spPred, const float4 *__restrict__ recA,
-                                                             float4 *__restrict__ recB) {
+                                                             unsigned *__restrict__ bMask, unsigned *__restrict__ elasticMask) {
   using G = LaneGeom<L>;
   __shared__ float term[6 * G::CS];
   pdl_entry();
@@ -38,6 +38,7 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
   const bool live = id < d.N;
   float4 pi = f4(0.f, 0.f, 0.f, 0.f), vi = pi;
   bool active = false;
+  unsigned bmask = 0u, emask = 0u;
   if (live) {
     pi = sp[id];
     active = !is_boundary(sortedType[id]);
@@ -53,6 +54,10 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
 #pragma unroll
     for (int i = 0; i < G::SLOTS; i++) {
       float a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (jd[i] != SPH_NO_ID) {  // type masks of the neighbour list for the integration / membrane kernels (see k_forces)
+        if (is_boundary(Pj[i].w)) bmask |= 1u << (l + L * i);
+        if ((int)Pj[i].w == SPH_ELASTIC_PARTICLE) emask |= 1u << (l + L * i);
+      }
       if (jd[i] != SPH_NO_ID && !forces_term(d, pi, vi, Pj[i], Vj[i], a[0], a[1], a[2], a[3], a[4], a[5]))
         a[0] = a[1] = a[2] = a[3] = a[4] = a[5] = 0.f;
       float *o = term + pl * G::S + l + L * i;
@@ -73,13 +78,17 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
               sz = __shfl_sync(0xffffffffu, s, base + 2);
   const float tx = __shfl_sync(0xffffffffu, u, base), ty = __shfl_sync(0xffffffffu, u, base + 1),
               tz = __shfl_sync(0xffffffffu, u, base + 2);
+#pragma unroll
+  for (int o = 1; o < L; o <<= 1) {
+    bmask |= __shfl_xor_sync(0xffffffffu, bmask, o);
+    emask |= __shfl_xor_sync(0xffffffffu, emask, o);
+  }
   if (!live || l != 0) return;
   const float4 zero = f4(0.f, 0.f, 0.f, 0.f);
   if (!active) {  // boundary particle, as in k_forces
     acc[id] = zero;
     acc[d.N + id] = zero;
     pressure[id] = 0.f;
-    recB[2 * (size_t)id + 1] = zero;
     spPred[id] = pi;
     return;
   }
@@ -90,7 +99,8 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
   acc[id] = a;
   acc[d.N + id] = zero;
   pressure[id] = 0.f;
-  recB[2 * (size_t)id + 1] = zero;
+  bMask[id] = bmask;
+  if (elasticMask) elasticMask[id] = emask;
   spPred[id] = predict_position(d, pi, vi, zero);
 }
 
@@ -133,9 +143,10 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_predict_density_lanes(DevPar
   rho[d.N + id] = rhoP;
   float p_corr = (rhoP - d.rho0) * d.delta;  // :1093-1096
   if (p_corr < 0.f) p_corr = 0.f;
-  const float p = recB[2 * (size_t)id + 1].x + p_corr;
-  pressure[id] = p;
-  recB[2 * (size_t)id + 1] = f4(p, rhoP, 0.f, 0.f);
+  float4 rec = recB[id];
+  rec.w += p_corr;
+  pressure[id] = rec.w;
+  recB[id] = rec;
 }
 
 // computePressureForceAcceleration + predictPositions (MODE 1) or + integrate (MODE 2): k_pressure_force<MODE, .>
@@ -149,8 +160,10 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevPara
                                                                      const uint2 *__restrict__ particleIndex,
                                                                      float4 *__restrict__ position,
                                                                      float4 *__restrict__ velocity,
-                                                                     unsigned *__restrict__ elasticMask,
-                                                                     int *__restrict__ memList, int *__restrict__ memCount) {
+                                                                     const unsigned *__restrict__ elasticMask,
+                                                                     int *__restrict__ memList, int *__restrict__ memCount,
+                                                                     const unsigned *__restrict__ bMask,
+                                                                     const float *__restrict__ rhoP) {
   using G = LaneGeom<L>;
   __shared__ float term[3 * G::CS];
   pdl_entry();
@@ -164,28 +177,22 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevPara
     active = !is_boundary(pi.w);
   }
   float rho_i = 1.f;
-  unsigned bmask = 0, emask = 0;
   if (active) {
-    const float4 ti = recB[2 * (size_t)id + 1];
-    const float p_i = ti.x;
-    rho_i = ti.y;
+    const float p_i = recB[id].w;
+    rho_i = rhoP[id];
     const float closeThr = (float)d.closeThr;
     const float hq = d.hScaled * 0.25f;
     int jd[G::SLOTS];
-    float4 Pj[G::SLOTS], Qj[G::SLOTS];
+    float4 Pj[G::SLOTS];
 #pragma unroll
     for (int i = 0; i < G::SLOTS; i++) jd[i] = __ldg(nb + nb_index(id, l + L * i));
 #pragma unroll
-    for (int i = 0; i < G::SLOTS; i++) ld256(recB + 2 * (size_t)(jd[i] != SPH_NO_ID ? jd[i] : id), Pj[i], Qj[i]);
+    for (int i = 0; i < G::SLOTS; i++) Pj[i] = ldg4(recB + (jd[i] != SPH_NO_ID ? jd[i] : id));
 #pragma unroll
     for (int i = 0; i < G::SLOTS; i++) {
       const int k = l + L * i;
       float ax = 0.f, ay = 0.f, az = 0.f;
-      if (jd[i] != SPH_NO_ID) {
-        if (MODE == 2 && is_boundary(Pj[i].w)) bmask |= 1u << k;
-        if (MODE == 2 && (int)Pj[i].w == SPH_ELASTIC_PARTICLE) emask |= 1u << k;
-        if (!pressure_term(d, pi, p_i, Pj[i], Qj[i].x, Qj[i].y, closeThr, hq, ax, ay, az)) ax = ay = az = 0.f;
-      }
+      if (jd[i] != SPH_NO_ID && !pressure_term(d, pi, p_i, Pj[i], Pj[i].w, rhoP, jd[i], closeThr, hq, ax, ay, az)) ax = ay = az = 0.f;
       float *o = term + pl * G::S + k;
       o[0] = ax; o[G::CS] = ay; o[2 * G::CS] = az;
     }
@@ -200,13 +207,6 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevPara
   const int base = (t & 31) - l;
   const float rx = __shfl_sync(0xffffffffu, s, base), ry = __shfl_sync(0xffffffffu, s, base + 1),
               rz = __shfl_sync(0xffffffffu, s, base + 2);
-  if (MODE == 2) {
-#pragma unroll
-    for (int o = 1; o < L; o <<= 1) {
-      bmask |= __shfl_xor_sync(0xffffffffu, bmask, o);
-      emask |= __shfl_xor_sync(0xffffffffu, emask, o);
-    }
-  }
   if (!live || l != 0) return;
   if (!active) {
     acc[d.N + id] = f4(0.f, 0.f, 0.f, 0.f);  // :1126-1129
@@ -218,9 +218,9 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_pressure_force_lanes(DevPara
   if (MODE == 1) spPred[id] = predict_position(d, sp[id], sv[id], result);
   if (MODE == 2) {
     const unsigned serial = particleIndex[id].y;
-    integrate_particle(d, id, sp[id], sv[id], acc[id] + result, pi.w, serial, bmask, spT, sv, nb, position, velocity,
+    integrate_particle(d, id, sp[id], sv[id], acc[id] + result, pi.w, serial, bMask[id], spT, sv, nb, position, velocity,
                        /*foldFinalize=*/elasticMask == nullptr);
-    if (elasticMask) membrane_prologue(d, id, serial, emask, pi.w, elasticMask, memList, memCount, position, velocity);
+    if (elasticMask) membrane_prologue(d, id, serial, elasticMask[id], pi.w, memList, memCount, position, velocity);
   }
 }
 
@@ -229,7 +229,7 @@ template <int L> static inline int lanes_grid(int n) { return (n + LaneGeom<L>::
 
 bool launch_forces_lanes(sph_ctx *c, int L) {
   float4 *pred = c->sortedPosition + c->d.N;
-#define F_ARGS c->d, c->sortedPosition, c->sortedVelocity, c->sortedType, c->nbIds, c->rho, c->acceleration, c->pressure, pred, c->recA, c->recB
+#define F_ARGS c->d, c->sortedPosition, c->sortedVelocity, c->sortedType, c->nbIds, c->rho, c->acceleration, c->pressure, pred, c->recA, c->bMask, c->elasticMask
   if (L == 4) launch_k(c, k_forces_lanes<4>, dim3(lanes_grid<4>(c->d.N)), dim3(LaneGeom<4>::T), F_ARGS);
   else if (L == 8) launch_k(c, k_forces_lanes<8>, dim3(lanes_grid<8>(c->d.N)), dim3(LaneGeom<8>::T), F_ARGS);
   else if (L == 16) launch_k(c, k_forces_lanes<16>, dim3(lanes_grid<16>(c->d.N)), dim3(LaneGeom<16>::T), F_ARGS);
@@ -252,7 +252,7 @@ bool launch_predict_density_lanes(sph_ctx *c, int L) {
 bool launch_pressure_force_lanes(sph_ctx *c, int mode, int L) {
   float4 *pred = c->sortedPosition + c->d.N;
 #define P_ARGS c->d, c->spT, c->sortedVelocity, c->nbIds, c->recB, c->acceleration, c->sortedPosition, pred, c->particleIndex, \
-               c->position, c->velocity, c->elasticMask, c->memList, c->memCount
+               c->position, c->velocity, c->elasticMask, c->memList, c->memCount, c->bMask, (const float *)(c->rho + c->d.N)
 #define P_LAUNCH(M, LL) launch_k(c, k_pressure_force_lanes<M, LL>, dim3(lanes_grid<LL>(c->d.N)), dim3(LaneGeom<LL>::T), P_ARGS)
   if (mode != 1 && mode != 2) return false;
   if (L == 4) { if (mode == 1) P_LAUNCH(1, 4); else P_LAUNCH(2, 4); }

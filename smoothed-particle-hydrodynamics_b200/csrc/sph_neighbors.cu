@@ -249,6 +249,9 @@ __device__ __forceinline__ void ld256u(const void *p, uint4 &a, uint4 &b) {
                : "l"(p));
 }
 
+struct LpYes { static constexpr bool value = true; };
+struct LpNo { static constexpr bool value = false; };
+
 template <bool WITH_DENSITY, int VAR>
 __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(DevParams d, const float4 *__restrict__ sp,
                                                                     const float *__restrict__ S,
@@ -501,13 +504,15 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   // nsStats[1], set by k_hash_count from the number of particles that needed the histogram in the previous step.
   const bool histFirst = VAR != 2 || nsStats == nullptr || nsStats[1] != 0u;
   int within = 0;
-  auto first_pass = [&](unsigned hv) {
+  // HIST is a compile-time constant per call site: the loop without the histogram must not keep its four 64-bit
+  // accumulators alive (a run-time flag inside one loop cost 0.3 ms at 8 M particles)
+  auto first_pass = [&](unsigned hv, auto HIST) {
     const int j = hit_index(hv);
     if (j == id) return;
     const float dd = dist2(j);
     if (dd <= h2) {
       within++;
-      if (histFirst) hist_add(dd);
+      if (decltype(HIST)::value) hist_add(dd);
     }
     if (dd <= r2open && found < SPH_NB) take(j, dd);
   };
@@ -527,7 +532,8 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     return (curCode + (unsigned)i) & 0xffffu;
   };
   if (VAR == 2) {
-    for (int t = 0; t < n; t++) first_pass(next_hit());
+    if (histFirst) { for (int t = 0; t < n; t++) first_pass(next_hit(), LpYes()); }
+    else { for (int t = 0; t < n; t++) first_pass(next_hit(), LpNo()); }
     if (!histFirst && within >= SPH_NB) {   // the histogram decides r_thr after all: build it
       curMask = 0u;
       curEntry = 0;
@@ -540,8 +546,8 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     }
   } else {
     const int nList = min(n, LP_CAP);
-    for (int t = 0; t < nList; t++) first_pass(hits[t][tid]);
-    for (int t = LP_CAP; t < n; t++) first_pass(ovf[t - LP_CAP]);
+    for (int t = 0; t < nList; t++) first_pass(hits[t][tid], LpYes());
+    for (int t = LP_CAP; t < n; t++) first_pass(ovf[t - LP_CAP], LpYes());
   }
   int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
   {

@@ -113,7 +113,7 @@ template <int FIELD, bool PACK>
 __global__ void __launch_bounds__(256) k_slab_halo(int n, const int *__restrict__ list, int first,
                                                    const unsigned *__restrict__ back, float *__restrict__ rho,
                                                    float4 *__restrict__ recA, float4 *__restrict__ recB,
-                                                   float4 *__restrict__ spPred,
+                                                   float4 *__restrict__ spPred, float *__restrict__ rhoPred,
                                                    void *__restrict__ buf) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -125,8 +125,8 @@ __global__ void __launch_bounds__(256) k_slab_halo(int n, const int *__restrict_
   }
   if (FIELD == 1) {  // (p, rho*): second half of the pressure-force record
     float2 *b = (float2 *)buf;
-    float4 *q = recB + 2 * (size_t)sid + 1;
-    if (PACK) b[i] = make_float2(q->x, q->y); else *q = make_float4(b[i].x, b[i].y, 0.f, 0.f);
+    float *q = reinterpret_cast<float *>(recB + sid) + 3;   // pressure slot of the 16-byte record; rho* is rho[N + sid]
+    if (PACK) b[i] = make_float2(*q, rhoPred[sid]); else { *q = b[i].x; rhoPred[sid] = b[i].y; }
   }
   if (FIELD == 2) { float4 *b = (float4 *)buf; if (PACK) b[i] = spPred[sid]; else spPred[sid] = b[i]; }
 }
@@ -259,7 +259,7 @@ static int halo(sph_ctx *c, int field, int side, void *buf, bool pack) {
   const int *list = pack ? s->sendList[side] : nullptr;
   const int first = s->recvStart[side];
   float4 *pred = c->sortedPosition + c->d.N;
-#define H(F, P) k_slab_halo<F, P><<<nblk(n), 256, 0, c->stream>>>(n, list, first, c->particleIndexBack, c->rho, c->recA, c->recB, pred, buf)
+#define H(F, P) k_slab_halo<F, P><<<nblk(n), 256, 0, c->stream>>>(n, list, first, c->particleIndexBack, c->rho, c->recA, c->recB, pred, c->rho + c->d.N, buf)
   if (pack) { if (field == 0) H(0, true); else if (field == 1) H(1, true); else H(2, true); }
   else { if (field == 0) H(0, false); else if (field == 1) H(1, false); else H(2, false); }
 #undef H
@@ -520,14 +520,14 @@ struct SlabHaloSend {
 template <int FIELD>
 __global__ void __launch_bounds__(256) k_slab_halo_send(SlabHaloSend a, const unsigned *__restrict__ back,
                                                         const float *__restrict__ rho, const float4 *__restrict__ recB,
-                                                        const float4 *__restrict__ spPred) {
+                                                        const float4 *__restrict__ spPred, const float *__restrict__ rhoPred) {
   const int total = a.n[0] + a.n[1];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int side = i < a.n[0] ? 0 : 1;
     const int k = side ? i - a.n[0] : i;
     const unsigned sid = back[a.list[side][k]];
     if (FIELD == 0) ((float *)a.dst[side])[k] = rho[sid];
-    if (FIELD == 1) { const float4 q = recB[2 * (size_t)sid + 1]; ((float2 *)a.dst[side])[k] = make_float2(q.x, q.y); }
+    if (FIELD == 1) ((float2 *)a.dst[side])[k] = make_float2(recB[sid].w, rhoPred[sid]);
     if (FIELD == 2) ((float4 *)a.dst[side])[k] = spPred[sid];
   }
 }
@@ -545,7 +545,7 @@ template <int FIELD>
 __global__ void __launch_bounds__(256) k_slab_halo_recv(SlabHaloRecv a, const unsigned *__restrict__ back,
                                                         float *__restrict__ rho, float4 *__restrict__ recA,
                                                         float4 *__restrict__ recB, float4 *__restrict__ spPred,
-                                                        int *sticky) {
+                                                        float *__restrict__ rhoPred, int *sticky) {
   // the send kernel has completed (stream order): its stores are out, announce them; then wait for the neighbours'
   if (blockIdx.x == 0 && threadIdx.x < 2 && a.raise[threadIdx.x]) st_relaxed_sys(a.raise[threadIdx.x], a.epoch);
   if (threadIdx.x < 2 && a.flag[threadIdx.x]) wait_delivery(a.flag[threadIdx.x], a.epoch, sticky);
@@ -562,7 +562,8 @@ __global__ void __launch_bounds__(256) k_slab_halo_recv(SlabHaloRecv a, const un
     }
     if (FIELD == 1) {
       const float2 v = __ldcg((const float2 *)a.src[side] + k);
-      recB[2 * (size_t)sid + 1] = make_float4(v.x, v.y, 0.f, 0.f);
+      reinterpret_cast<float *>(recB + sid)[3] = v.x;
+      rhoPred[sid] = v.y;
     }
     if (FIELD == 2) spPred[sid] = __ldcg((const float4 *)a.src[side] + k);
   }
@@ -712,8 +713,8 @@ static int linked_halo(sph_ctx *c, int field) {
   b.epoch = s->epoch;
   float4 *pred = c->sortedPosition + c->d.N;
   const int gs = min(nblk(a.n[0] + a.n[1]), 4 * c->numSMs), gr = min(nblk(b.n[0] + b.n[1]), 4 * c->numSMs);
-#define SEND(F) k_slab_halo_send<F><<<gs, 256, 0, c->stream>>>(a, c->particleIndexBack, c->rho, c->recB, pred)
-#define RECV(F) k_slab_halo_recv<F><<<gr, 256, 0, c->stream>>>(b, c->particleIndexBack, c->rho, c->recA, c->recB, pred, s->doneCounter + 1)
+#define SEND(F) k_slab_halo_send<F><<<gs, 256, 0, c->stream>>>(a, c->particleIndexBack, c->rho, c->recB, pred, c->rho + c->d.N)
+#define RECV(F) k_slab_halo_recv<F><<<gr, 256, 0, c->stream>>>(b, c->particleIndexBack, c->rho, c->recA, c->recB, pred, c->rho + c->d.N, s->doneCounter + 1)
   ProfMark pm = prof_mark_begin(c, PK_SLAB_HALO);
   if (field == 0) { SEND(0); RECV(0); } else if (field == 1) { SEND(1); RECV(1); } else { SEND(2); RECV(2); }
   prof_mark_end(c, pm);

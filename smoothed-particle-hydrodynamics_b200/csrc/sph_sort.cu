@@ -27,12 +27,12 @@ __global__ void __launch_bounds__(256) k_hash_count(DevParams d, const float4 *_
                                                     uint2 *__restrict__ particleIndex,
                                                     unsigned long long *__restrict__ scanState,
                                                     unsigned *__restrict__ scanTicket, int scanTiles,
-                                                    unsigned *__restrict__ nsStats) {
+                                                    unsigned *__restrict__ nsStats, unsigned histPct) {
   pdl_entry();
   int id = blockIdx.x * blockDim.x + threadIdx.x;
-  // neighbour search of this step: histogram in the first pass if more than a quarter of the particles needed it in
+  // neighbour search of this step: histogram in the first pass if more than histPct % of the particles needed it in
   // the previous step (see k_find_neighbors_list); then restart the count
-  if (id == 0) { nsStats[1] = (4ull * nsStats[0] > (unsigned long long)d.N) ? 1u : 0u; nsStats[0] = 0u; }
+  if (id == 0) { nsStats[1] = (100ull * nsStats[0] > (unsigned long long)histPct * (unsigned long long)d.N) ? 1u : 0u; nsStats[0] = 0u; }
   // reset the look-back scan of this step's sort (k_scan_cells runs after this kernel): the step's launch
   // parameters are then the same every step, which is what lets sph_step replay a captured CUDA graph
   for (int t = id; t < scanTiles; t += gridDim.x * blockDim.x) scanState[t] = 0ull;
@@ -193,8 +193,7 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
     const float4 v = velocity[serial];
     recA[2 * (size_t)dst] = p;
     recA[2 * (size_t)dst + 1] = f4(v.x, v.y, v.z, 0.f);  // .w = rho(t), set by the neighbour search
-    recB[2 * (size_t)dst] = p;
-    recB[2 * (size_t)dst + 1] = f4(0.f, 0.f, 0.f, 0.f);
+    recB[dst] = f4(p.x, p.y, p.z, 0.f);   // (x, y, z, pressure = 0): computeForcesAndInitPressure's pressure[id] = 0 (:697)
     p.w = (float)(int)cell;
     sortedVelocity[dst] = v;
     sortedPosition[dst] = p;
@@ -241,10 +240,10 @@ void launch_hash_count(sph_ctx *c, bool write_pairs) {
   c->cellCountClean = false;
   if (write_pairs)
     launch_k(c, k_hash_count<true>, dim3(blocks_for(N, 256)), dim3(256), c->d, c->position, c->key, c->cellCount,
-             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles, c->nsStats);
+             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles, c->nsStats, c->hist_pct);
   else
     launch_k(c, k_hash_count<false>, dim3(blocks_for(N, 256)), dim3(256), c->d, c->position, c->key, c->cellCount,
-             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles, c->nsStats);
+             c->particleIndex, c->scanState, c->scanTicket, c->scanTiles, c->nsStats, c->hist_pct);
 }
 
 void launch_sort(sph_ctx *c, bool fuse_reorder) {

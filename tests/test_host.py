@@ -397,7 +397,9 @@ def test_simulator_config_bprime_from_files(tmp_path):
     L.ow_sim_set_muscle_hook(sim, 0)
     p = common.fill_counts(O.default_params(box=(36, 24, 54.5)), pos)
     p.elastic_offset = p.num_boundary
-    o = O.create(p, pos, vel, elastic=con)
+    # the springs as the loader sees them: %e text keeps 7 significant digits of the rest lengths
+    con_txt = np.loadtxt(d / "elasticconnections.txt", dtype=np.float32).reshape(-1, 4)
+    o = O.create(p, pos, vel, elastic=con_txt)
     for s in range(4):
         L.ow_sim_step(sim, 0)
         o.step()
