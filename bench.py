@@ -279,6 +279,10 @@ def time_facade(name, scene, steps, device=0, run_ahead=True):
     return ms, ok
 
 
+PRESSURE_FRAC_MAIN = None
+LAST_PRESSURE_FRAC = None    # fraction of particles with non-zero pressure at the end of the last timed run
+
+
 def time_device(L, name, scene, steps, warmup, device=0, profile=False):
     """Device-timed fused steps of one scene on one GPU (CUDA events on the library's stream, state resident in
     HBM). profile=True adds the per-kernel events (large scenes only: they disable the CUDA-graph replay)."""
@@ -295,7 +299,8 @@ def time_device(L, name, scene, steps, warmup, device=0, profile=False):
         prof = ctx.profile_report()
         ctx.profile(False)
     fin = bool(np.isfinite(ctx.read("position", len(pos))[:, :3]).all())
-    global LAST_CHAIN_FLOOR_MS
+    global LAST_CHAIN_FLOOR_MS, LAST_PRESSURE_FRAC
+    LAST_PRESSURE_FRAC = float((ctx.read("pressure") > 0).mean())
     LAST_CHAIN_FLOOR_MS = ctx.empty_chain_ms(max(1, launches // max(1, steps))) if len(pos) <= (1 << 21) else None
     ctx.close()
     return ms / steps, launches, prof, fin
@@ -518,13 +523,21 @@ def config_block(L, local, args):
         steps, e2e_steps, cpu_steps = plan[name]
         scene = make_workload(name, L)
         n = len(scene[1])
+        if name == "dambreak_1m":
+            # the same scene 2000 steps later (the block has collapsed, pressure everywhere): the pressure-force kernel
+            # drops pairs without pressure before the sqrt / divisions, and a fluid at rest has nothing but such pairs
+            ms_late = time_device(L, name, scene, steps, 2000, device=local)[0]
+            late = {"ms_per_step": ms_late, "value": n / (ms_late * 1e-3), "pressure_nonzero_frac": LAST_PRESSURE_FRAC}
         ms, launches, _, fin = time_device(L, name, scene, steps, 5, device=local)
         e2e_ms, ok = time_facade(name, scene, e2e_steps, device=local)
         blk_ms, _ = time_facade(name, scene, e2e_steps, device=local, run_ahead=False)
         row = {"workload": name, "particles": n, "ms_per_step": ms, "value": n / (ms * 1e-3),
                "e2e_value": n / (e2e_ms * 1e-3), "e2e_ms_per_step": e2e_ms,
                "e2e_blocking_value": n / (blk_ms * 1e-3), "gpu_launches_per_step": launches / steps,
-               "empty_kernel_chain_ms": LAST_CHAIN_FLOOR_MS, "finite": fin and ok}
+               "empty_kernel_chain_ms": LAST_CHAIN_FLOOR_MS, "pressure_nonzero_frac": LAST_PRESSURE_FRAC,
+               "finite": fin and ok}
+        if name == "dambreak_1m":
+            row["after_2000_steps"] = late
         if not args.no_cpu_baseline:
             cb, cpu_ms, _ = time_cpu(name, cpu_steps, 1, scene=scene[:3])
             row.update(cpu_value=cb["value"], cpu_ms_per_step=cpu_ms, cpu_kind=cb["kind"], cpu_cores=cb["cores"],
@@ -613,6 +626,8 @@ def main():
         sampler.start()
         big = n > (1 << 21)   # per-kernel events cost nothing at 8 M particles; small scenes replay a CUDA graph instead
         ms, launches, prof, fin = time_device(L, args.workload, scene, steps, warmup, device=local, profile=big)
+        global PRESSURE_FRAC_MAIN
+        PRESSURE_FRAC_MAIN = LAST_PRESSURE_FRAC
         clocks = sampler.stop()
         if not big:
             prof = time_device(L, args.workload, scene, steps, warmup, device=local, profile=True)[2]
@@ -645,6 +660,8 @@ def main():
                     "d2h_bytes_per_step": 16 * n, "ms_per_step": e2e_ms, "steps": e2e_steps, "mode": e2e_mode,
                     "blocking_value": total / (e2e_blocking_ms * 1e-3), "blocking_ms_per_step": e2e_blocking_ms},
             "gpu_launches": launches, "roofline": roof}
+    if world == 1:
+        line["config"]["pressure_nonzero_frac"] = PRESSURE_FRAC_MAIN
     line.update(extra)
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:   # cross-check of the reference arm, same scene, a few steps

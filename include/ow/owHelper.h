@@ -30,6 +30,12 @@ class owHelper {
   static bool loadMembranes(int *&membraneData_cpp, int &numOfMembranes, int *&particleMembranesList_cpp, int numOfElasticP);
   static void loadConfigurationToFile(float *position, float *connections = 0, int *membranes = 0,
                                       bool firstIteration = true);  // owHelper.cpp:1640-1672
+  // Additions: the same recording off the caller's thread. The frame is copied (positions only: connections and
+  // membranes belong to the first frame and must stay alive until flushRecording()), a writer thread formats and
+  // appends it in order; flushRecording() blocks until everything queued is on disk.
+  static void loadConfigurationToFileAsync(const float *position, float *connections = 0, int *membranes = 0,
+                                           bool firstIteration = true);
+  static void flushRecording();
   static void loadConfigurationFromFile(float *&position, float *&connections, int *&membranes,
                                         int iteration = 0);  // owHelper.cpp:1674-1740
   static void log_bufferf(const float *buffer, const int element_size, const int global_size, const char *fileName);

@@ -97,7 +97,7 @@ def build_host(force=False, verbose=False):
     pyinc = sysconfig.get_paths()["include"]
     pyver = "python%d.%d" % sys.version_info[:2]
     common = ["g++", "-std=c++17", "-O2", "-fPIC", "-Wall", "-I", INC, "-I", pyinc]
-    link = ["-L", PKG, "-lsph_b200", "-Wl,-rpath,$ORIGIN", "-l" + pyver, "-ldl", "-lm"]
+    link = ["-L", PKG, "-lsph_b200", "-Wl,-rpath,$ORIGIN", "-l" + pyver, "-ldl", "-lm", "-lpthread"]
     def run(cmd):
         if verbose:
             print("[build]", " ".join(cmd))

@@ -10,6 +10,10 @@
 #include <iostream>
 #include <stdexcept>
 #include <vector>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
 
 #include "ow/owOpenCLSolver.h"
 
@@ -191,9 +195,54 @@ void owHelper::loadConfigurationToFile(float *position, float *connections, int 
   }
 }
 
+// ---- asynchronous recording: one writer thread, frames in call order ----
+namespace {
+struct RecJob { std::vector<float> position; float *connections; int *membranes; bool first; };
+std::mutex g_rec_mu;
+std::condition_variable g_rec_cv, g_rec_idle;
+std::deque<RecJob> g_rec_q;
+bool g_rec_busy = false, g_rec_started = false;
+void rec_worker() {
+  for (;;) {
+    RecJob job;
+    {
+      std::unique_lock<std::mutex> lk(g_rec_mu);
+      g_rec_cv.wait(lk, [] { return !g_rec_q.empty(); });
+      job = std::move(g_rec_q.front());
+      g_rec_q.pop_front();
+      g_rec_busy = true;
+    }
+    owHelper::loadConfigurationToFile(job.position.data(), job.connections, job.membranes, job.first);
+    {
+      std::lock_guard<std::mutex> lk(g_rec_mu);
+      g_rec_busy = false;
+    }
+    g_rec_idle.notify_all();
+  }
+}
+}  // namespace
+
+void owHelper::loadConfigurationToFileAsync(const float *position, float *connections, int *membranes, bool firstIteration) {
+  RecJob job;
+  job.position.assign(position, position + 4 * (size_t)PARTICLE_COUNT);
+  job.connections = connections; job.membranes = membranes; job.first = firstIteration;
+  {
+    std::lock_guard<std::mutex> lk(g_rec_mu);
+    if (!g_rec_started) { std::thread(rec_worker).detach(); g_rec_started = true; }
+    g_rec_q.push_back(std::move(job));
+  }
+  g_rec_cv.notify_one();
+}
+
+void owHelper::flushRecording() {
+  std::unique_lock<std::mutex> lk(g_rec_mu);
+  g_rec_idle.wait(lk, [] { return g_rec_q.empty() && !g_rec_busy; });
+}
+
 // Playback reader (owHelper.cpp:1674-1740): frame `iteration` of position_buffer.txt; connections and
 // membranes on iteration 0. Sets PARTICLE_COUNT = Ne + Nl and iterationCount = number of frames.
 void owHelper::loadConfigurationFromFile(float *&position, float *&connections, int *&membranes, int iteration) {
+  flushRecording();
   try {
     if (iteration == 0) {
       f_data.clear();

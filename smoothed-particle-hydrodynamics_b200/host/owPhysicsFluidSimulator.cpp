@@ -107,9 +107,9 @@ void owPhysicsFluidSimulator::finishStepOutput(bool load_to) {
     printf("_Total_step_time:\t%9.3f ms\n", helper->get_elapsedTime());
     printf("------------------------------------\n");
   }
-  if (load_to) {
-    if (iterationCount == 0) owHelper::loadConfigurationToFile(position_cpp, elasticConnectionsData_cpp, membraneData_cpp);
-    else if (iterationCount % iter_step == 0) owHelper::loadConfigurationToFile(position_cpp, NULL, NULL, false);
+  if (load_to) {  // formatted and written by owHelper's writer thread (the frame is copied): a 61 k-particle frame is ~20 ms of text
+    if (iterationCount == 0) owHelper::loadConfigurationToFileAsync(position_cpp, elasticConnectionsData_cpp, membraneData_cpp);
+    else if (iterationCount % iter_step == 0) owHelper::loadConfigurationToFileAsync(position_cpp, NULL, NULL, false);
   }
 }
 
@@ -194,6 +194,7 @@ double owPhysicsFluidSimulator::simulationStep(const bool load_to) {
 }
 
 owPhysicsFluidSimulator::~owPhysicsFluidSimulator(void) {
+  owHelper::flushRecording();  // queued frames reference elasticConnectionsData_cpp / membraneData_cpp
   if (position_cpp) sph_host_free(position_cpp);
   delete[] velocity_cpp;
   delete[] density_cpp;

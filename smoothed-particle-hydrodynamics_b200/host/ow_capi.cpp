@@ -13,6 +13,7 @@ void ow_set_slab_devices(const int *ordinals, int n) { owSetSlabDevices(ordinals
 void ow_set_quiet(int q) { owHelper::quiet = q != 0; }
 void ow_set_configuration_files(const char *dir, const char *pos, const char *vel) { owHelper::setConfigurationFiles(dir, pos, vel); }
 void ow_set_buffers_dir(const char *dir) { owHelper::setBuffersDir(dir); }
+void ow_flush_recording(void) { owHelper::flushRecording(); }
 
 struct ow_sim { owHelper *helper; owPhysicsFluidSimulator *sim; };
 

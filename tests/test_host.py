@@ -222,6 +222,7 @@ def test_simulator_from_configuration_files_and_l_to(tmp_path):
         o.step()
     got = np.ctypeslib.as_array(L.ow_sim_position(sim), shape=(len(cfg["position"]), 4))
     assert common.first_mismatch(got, o.read("position", len(got))) is None
+    L.ow_flush_recording()   # frames are written by a background thread
     lines = [x for x in open(tmp_path / "buffers" / "position_buffer.txt").read().split("\n") if x]
     nl = int(cfg["params"].num_liquid)
     assert int(lines[0]) == 0 and int(lines[1]) == nl
