@@ -50,7 +50,7 @@ KERNEL_BYTES = {
     "hash_count": 24,
     "sort(scan+scatter+rank_reorder)": 16 + 76 + 8,
     "find_neighbors+density": 256 + 272 + 264,
-    "forces+predict0": 356 + 92,
+    "forces+predict0+density0": 356 + 92 + 280 + 16,
     "elastic": 0,
     "predict_density+correct_pressure": 280 + 16,
     "pressure_force+predict": 324 + 92,
@@ -62,7 +62,7 @@ KERNEL_LIMITER = {
     "find_neighbors+density": "l1-data-pipe+issue",
     "pressure_force+predict": "l1-data-pipe+issue",
     "pressure_force+integrate": "l1-data-pipe+issue",
-    "forces+predict0": "l1-data-pipe",
+    "forces+predict0+density0": "l1-data-pipe",
     "predict_density+correct_pressure": "l1-data-pipe+hbm",
     "sort(scan+scatter+rank_reorder)": "hbm",
     "hash_count": "hbm",
@@ -70,7 +70,7 @@ KERNEL_LIMITER = {
 # profile name -> kernel whose ncu capture (profiles/*_ncu_full_summary.json) gives the measured DRAM traffic per launch
 NCU_KERNEL = {"find_neighbors+density": "k_find_neighbors_list<1,2>", "pressure_force+predict": "k_pressure_force<1,0>",
               "pressure_force+integrate": "k_pressure_force<2,0>", "predict_density+correct_pressure": "k_predict_density<1,0>",
-              "forces+predict0": "k_forces<1,0>"}
+              "forces+predict0+density0": "k_forces<1,0>"}
 
 
 def measured_traffic(kernel, particles):
@@ -220,6 +220,7 @@ def run_reference(args, rank):
 
 # ---------------------------------------------------------------- the drop-in C++ class (libow_b200.so)
 _FACADE = None
+TRANSPORT_USED = None
 LAST_CHAIN_FLOOR_MS = None   # dependent chain of as many EMPTY kernels as the last timed step had (small scenes)
 
 
@@ -339,10 +340,16 @@ def make_transport(slab, torch, r, dev):
     """Default: peer-memory links (the neighbours' kernels write straight into this rank's mailbox over NVLink; the
     whole step runs inside the library). SPH_SLAB_TRANSPORT=nccl selects the round-1 path: pack kernels, NCCL
     point-to-point sends issued from Python, unpack kernels."""
-    if os.environ.get("SPH_SLAB_TRANSPORT", "p2p") == "nccl":
+    global TRANSPORT_USED
+    tr = None
+    if os.environ.get("SPH_SLAB_TRANSPORT", "p2p") != "nccl":
+        tr = slab.PeerTransport.distributed(r)
+        TRANSPORT_USED = "p2p (peer-memory links over NVLink, no NCCL on the data path)"
+    if tr is None:   # asked for, or some rank could not map its neighbour's mailbox
+        TRANSPORT_USED = "nccl point-to-point" + ("" if os.environ.get("SPH_SLAB_TRANSPORT") == "nccl" else " (FALLBACK: peer mapping failed)")
         r.set_stream(torch.cuda.current_stream().cuda_stream)  # kernels and NCCL transfers ordered on one stream
-        return slab.DistTransport(r, dev)
-    return slab.PeerTransport.distributed(r)
+        tr = slab.DistTransport(r, dev)
+    return tr
 
 
 def time_slab(slab, torch, dist, L, r, tr, warmup, steps, e2e=True):
@@ -492,6 +499,33 @@ def slab_parity_check(slab, torch, dist, L, rank, world, local, steps=10):
     return verdict[0]
 
 
+def time_pressurised(L, name, scene, device=0, chunk=100, max_steps=1500, want_frac=0.5, steps=30):
+    """The same scene later, when the fluid carries pressure: the pressure-force kernel drops pairs without pressure
+    before the sqrt / divisions, and a fluid at rest (the bench scene during its first steps) has nothing but such pairs.
+    Steps in chunks until half of the particles have a non-zero pressure (or max_steps), watching the library's
+    out-of-grid / NaN counter so that a diverging run is never stepped on; then times `steps` steps."""
+    p, pos, vel = scene[:3]
+    ctx = L.create(p, pos, vel, device=device, **EXTRA.get(name, {}))
+    done, frac, healthy = 0, 0.0, True
+    while done < max_steps:
+        ctx.run_steps(chunk)
+        done += chunk
+        if ctx.out_of_grid_count() != 0:
+            healthy = False
+            break
+        frac = float((ctx.read("pressure") > 0).mean())
+        if frac >= want_frac:
+            break
+    out = {"steps_before": done, "pressure_nonzero_frac": frac, "healthy": healthy}
+    if healthy:
+        ms = ctx.run_steps(steps) / steps
+        healthy = ctx.out_of_grid_count() == 0
+        out.update(ms_per_step=ms, value=len(pos) / (ms * 1e-3), healthy=healthy,
+                   pressure_nonzero_frac=float((ctx.read("pressure") > 0).mean()))
+    ctx.close()
+    return out
+
+
 def roofline_of(prof, n, ms_total_region, value_per_gpu, world):
     """Roofline object of the dominant kernel (per-kernel CUDA events recorded inside the timed region)."""
     peak, peak_src = peaks()
@@ -524,10 +558,7 @@ def config_block(L, local, args):
         scene = make_workload(name, L)
         n = len(scene[1])
         if name == "dambreak_1m":
-            # the same scene 2000 steps later (the block has collapsed, pressure everywhere): the pressure-force kernel
-            # drops pairs without pressure before the sqrt / divisions, and a fluid at rest has nothing but such pairs
-            ms_late = time_device(L, name, scene, steps, 2000, device=local)[0]
-            late = {"ms_per_step": ms_late, "value": n / (ms_late * 1e-3), "pressure_nonzero_frac": LAST_PRESSURE_FRAC}
+            late = time_pressurised(L, name, scene, device=local)
         ms, launches, _, fin = time_device(L, name, scene, steps, 5, device=local)
         e2e_ms, ok = time_facade(name, scene, e2e_steps, device=local)
         blk_ms, _ = time_facade(name, scene, e2e_steps, device=local, run_ahead=False)
@@ -537,7 +568,7 @@ def config_block(L, local, args):
                "empty_kernel_chain_ms": LAST_CHAIN_FLOOR_MS, "pressure_nonzero_frac": LAST_PRESSURE_FRAC,
                "finite": fin and ok}
         if name == "dambreak_1m":
-            row["after_2000_steps"] = late
+            row["later_with_pressure"] = late
         if not args.no_cpu_baseline:
             cb, cpu_ms, _ = time_cpu(name, cpu_steps, 1, scene=scene[:3])
             row.update(cpu_value=cb["value"], cpu_ms_per_step=cpu_ms, cpu_kind=cb["kind"], cpu_cores=cb["cores"],
@@ -654,7 +685,7 @@ def main():
                        "state (%.0f MB) FITS in L2: not a bench configuration" % (n * 424 / 1e6),
                        "multi_gpu": "none" if world == 1 else
                        "one fluid, %d z-slabs, ghost layers + per-stage halo refresh + migration; transport: %s" %
-                       (world, os.environ.get("SPH_SLAB_TRANSPORT", "p2p (peer-memory links over NVLink, no NCCL on the data path)"))},
+                       (world, TRANSPORT_USED)},
             "clocks": clocks,
             "e2e": {"value": total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 400,
                     "d2h_bytes_per_step": 16 * n, "ms_per_step": e2e_ms, "steps": e2e_steps, "mode": e2e_mode,

@@ -114,6 +114,8 @@ class SphLib:
             L.sph_host_free.argtypes = [C.c_void_p]
             L.sph_host_free.restype = None
             L.sph_timer_start.argtypes = [C.c_void_p]
+            L.sph_out_of_grid_count.argtypes = [C.c_void_p]
+            L.sph_out_of_grid_count.restype = C.c_longlong
             L.sph_empty_chain_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, P(C.c_float)]
             L.sph_timer_stop.argtypes = [C.c_void_p, P(C.c_float)]
 
@@ -221,6 +223,9 @@ class SphContext:
         ms = C.c_float(0)
         self.L.check(self.L.lib.sph_empty_chain_ms(self.h, int(nodes), int(blocks), int(threads), int(replays), C.byref(ms)), "sph_empty_chain_ms")
         return float(ms.value)
+
+    def out_of_grid_count(self):
+        return int(self.L.lib.sph_out_of_grid_count(self.h))
 
     def profile(self, on):
         self.L.check(self.L.lib.sph_profile_enable(self.h, 1 if on else 0), "sph_profile_enable")

@@ -305,7 +305,7 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
   A(dalloc(&c->fnDeferred, N));
   A(dalloc(&c->scanState, (size_t)c->scanTiles));
   A(dalloc(&c->scanTicket, 1));
-  A(dalloc(&c->nsStats, 2));
+  A(dalloc(&c->nsStats, 4));
   if (ok) A(cudaMemcpy(c->position, pos4, 16 * N, cudaMemcpyHostToDevice));   // owOpenCLSolver.cpp:65
   if (ok) A(cudaMemcpy(c->velocity, vel4, 16 * N, cudaMemcpyHostToDevice));   // :66
   if (ok && c->has_membranes) {                                                // :70-71
@@ -379,7 +379,7 @@ enum { PK_HASH = 0, PK_SORT, PK_NEIGHBORS, PK_FORCES, PK_ELASTIC, PK_PREDICT_DEN
        PK_PRESSURE_FORCE_INTEGRATE, PK_MEMBRANES, PK_SLAB_RECORDS_, PK_SLAB_ABSORB_, PK_SLAB_HALO_, PK_COUNT };
 static_assert(PK_SLAB_RECORDS_ == PK_SLAB_RECORDS && PK_SLAB_ABSORB_ == PK_SLAB_ABSORB && PK_SLAB_HALO_ == PK_SLAB_HALO, "sph_ctx.h");
 static const char *const kProfNames[PK_COUNT] = {
-    "hash_count", "sort(scan+scatter+rank_reorder)", "find_neighbors+density", "forces+predict0", "elastic",
+    "hash_count", "sort(scan+scatter+rank_reorder)", "find_neighbors+density", "forces+predict0+density0", "elastic",
     "predict_density+correct_pressure", "pressure_force+predict", "pressure_force+integrate", "membranes",
     "slab:classify+deliver+wait_neighbours", "slab:absorb", "slab:halo_send+wait+recv"};
 
@@ -462,11 +462,11 @@ static int step_body(sph_ctx *c, int half) {
     { ProfScope s(c, PK_NEIGHBORS); launch_find_neighbors(c, true); }
     { ProfScope s(c, PK_FORCES); launch_forces(c, true); }
     if (elastic) { ProfScope s(c, PK_ELASTIC); launch_elastic(c); }
-    for (int it = 0; it < iters; it++) {
-      { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); }
+    for (int it = 0; it < iters; it++) {  // the density prediction of iteration 0 is part of the forces kernel
+      if (it > 0) { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); }
       if (it + 1 < iters) { ProfScope s(c, PK_PRESSURE_FORCE); launch_pressure_force(c, 1); }
     }
-    return 7 + (elastic ? 1 : 0) + 2 * iters - 1;
+    return 7 + (elastic ? 1 : 0) + 2 * iters - 2;
   }
   { ProfScope s(c, PK_PRESSURE_FORCE_INTEGRATE); launch_pressure_force(c, 2); }
   return 1 + fused_membranes(c);
@@ -551,10 +551,9 @@ int sph_step_part(sph_ctx *c, int part) {
       c->launches += 6;
       break;
     case 1:
-      { ProfScope s(c, PK_FORCES); launch_forces(c, true); }
+      { ProfScope s(c, PK_FORCES); launch_forces(c, true); }   // includes predictDensity + correctPressure of iteration 0
       if (c->d.numElastic > 0 && c->has_elastic) { ProfScope s(c, PK_ELASTIC); launch_elastic(c); c->launches++; }
-      { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); }
-      c->launches += 2;
+      c->launches += 1;
       break;
     case 2: { ProfScope s(c, PK_PRESSURE_FORCE); launch_pressure_force(c, 1); } c->launches++; break;
     case 3: { ProfScope s(c, PK_PREDICT_DENSITY); launch_predict_density(c, true); } c->launches++; break;
@@ -697,6 +696,17 @@ int sph_timer_stop(sph_ctx *c, float *elapsed_ms) {
 }
 
 long long sph_launch_count(const sph_ctx *c) { return c ? c->launches : 0; }
+
+// Particles that the hash found outside the grid or with a NaN coordinate since the context was created;
+// they are binned into the last cell, where a crowd of them makes the in-cell ranking quadratic. Synchronises.
+long long sph_out_of_grid_count(sph_ctx *c) {
+  if (!c) return -1;
+  unsigned v = 0;
+  if (cudaSetDevice(c->device) != cudaSuccess || cudaStreamSynchronize(c->stream) != cudaSuccess ||
+      cudaMemcpy(&v, c->nsStats + 2, 4, cudaMemcpyDeviceToHost) != cudaSuccess)
+    return -1;
+  return (long long)v;
+}
 
 // Pinned host memory for the read-back / upload buffers of the e2e path.
 void *sph_host_alloc(size_t bytes) {

@@ -11,40 +11,46 @@
 #include "sph_terms.cuh"
 
 #define LN_THREADS 256
+#ifndef LN_T4
+#define LN_T4 128
+#endif
 
 // shared-memory layout of the term table: element (component c, particle pl, slot k) at c * CS + pl * S + k with
 // S = 32 + L and CS = P * S + 1: the L x (32 / L) lanes of a warp write distinct banks, and so do the summing lanes.
 template <int L> struct LaneGeom {
-  static constexpr int T = L <= 4 ? 128 : LN_THREADS;  // threads per CTA (the L = 4 term table of 256 threads exceeds 48 KB)
+  static constexpr int T = L <= 4 ? LN_T4 : LN_THREADS;  // threads per CTA (the L = 4 term table of the forces kernel with 256 threads exceeds 48 KB)
   static constexpr int P = T / L;            // particles per CTA
   static constexpr int S = 32 + L;
   static constexpr int CS = P * S + 1;
   static constexpr int SLOTS = SPH_NB / L;    // slots per lane
 };
 
+// forces + predictPositions #0 + the first predictDensity / correctPressure (see k_forces<true, .>)
 template <int L>
 __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, const float4 *__restrict__ sp,
                                                              const float4 *__restrict__ sv,
                                                              const float *__restrict__ sortedType,
-                                                             const int *__restrict__ nb, const float *__restrict__ rho,
+                                                             const int *__restrict__ nb, float *__restrict__ rho,
                                                              float4 *__restrict__ acc, float *__restrict__ pressure,
                                                              float4 *__restrict__ spPred, const float4 *__restrict__ recA,
-                                                             unsigned *__restrict__ bMask, unsigned *__restrict__ elasticMask) {
+                                                             unsigned *__restrict__ bMask, unsigned *__restrict__ elasticMask,
+                                                             float4 *__restrict__ recB) {
   using G = LaneGeom<L>;
-  __shared__ float term[6 * G::CS];
+  static_assert(L >= 4, "lane 3 sums the density terms");
+  __shared__ float term[7 * G::CS];   // 3 viscosity + 3 surface tension + 1 predicted-density term per slot
   pdl_entry();
   const int t = threadIdx.x, pl = t / L, l = t % L;
   const int id = blockIdx.x * G::P + pl;
   const bool live = id < d.N;
-  float4 pi = f4(0.f, 0.f, 0.f, 0.f), vi = pi;
-  bool active = false;
+  const float4 zero = f4(0.f, 0.f, 0.f, 0.f);
+  float4 pi = zero, vi = zero, piP = zero;
+  bool active = false;   // not a boundary particle: takes part in the forces
   unsigned bmask = 0u, emask = 0u;
   if (live) {
     pi = sp[id];
     active = !is_boundary(sortedType[id]);
-  }
-  if (active) {
-    vi = sv[id];
+    if (active) vi = sv[id];
+    piP = active ? predict_position(d, pi, vi, zero) : pi;
     int jd[G::SLOTS];
     float4 Pj[G::SLOTS], Vj[G::SLOTS];
 #pragma unroll
@@ -53,25 +59,46 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
     for (int i = 0; i < G::SLOTS; i++) ld256(recA + 2 * (size_t)(jd[i] != SPH_NO_ID ? jd[i] : id), Pj[i], Vj[i]);
 #pragma unroll
     for (int i = 0; i < G::SLOTS; i++) {
-      float a[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (jd[i] != SPH_NO_ID) {  // type masks of the neighbour list for the integration / membrane kernels (see k_forces)
-        if (is_boundary(Pj[i].w)) bmask |= 1u << (l + L * i);
+      float a[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (jd[i] != SPH_NO_ID) {
+        const bool jBoundary = is_boundary(Pj[i].w);
+        // type masks of the neighbour list for the integration / membrane kernels (see k_forces)
+        if (jBoundary) bmask |= 1u << (l + L * i);
         if ((int)Pj[i].w == SPH_ELASTIC_PARTICLE) emask |= 1u << (l + L * i);
+        if (!density_term(d, piP, jBoundary ? Pj[i] : predict_position(d, Pj[i], Vj[i], zero), a[6])) a[6] = 0.f;
+        if (!active || !forces_term(d, pi, vi, Pj[i], Vj[i], a[0], a[1], a[2], a[3], a[4], a[5]))
+          a[0] = a[1] = a[2] = a[3] = a[4] = a[5] = 0.f;
       }
-      if (jd[i] != SPH_NO_ID && !forces_term(d, pi, vi, Pj[i], Vj[i], a[0], a[1], a[2], a[3], a[4], a[5]))
-        a[0] = a[1] = a[2] = a[3] = a[4] = a[5] = 0.f;
       float *o = term + pl * G::S + l + L * i;
 #pragma unroll
-      for (int c = 0; c < 6; c++) o[c * G::CS] = a[c];
+      for (int c = 0; c < 7; c++) o[c * G::CS] = a[c];
     }
   }
   __syncthreads();
-  // lane c < 3 sums component c of the viscosity sum and of the surface-tension sum, slots in order
+  // lane c < 3 sums component c of the viscosity sum and of the surface-tension sum, lane 3 the density terms (fp64),
+  // all over the slots in order
   float s = 0.f, u = 0.f;
   if (active && l < 3) {
     const float *a = term + l * G::CS + pl * G::S, *b = a + 3 * G::CS;
 #pragma unroll 8
     for (int k = 0; k < SPH_NB; k++) { s += a[k]; u += b[k]; }
+  }
+  if (live && l == 3) {
+    double density = 0.0;
+    const float *a = term + 6 * G::CS + pl * G::S;
+#pragma unroll 8
+    for (int k = 0; k < SPH_NB; k++) density += (double)a[k];
+    // predictDensity tail (:1054-1058) + correctPressure (:1093-1096) on pressure = 0 (:697)
+    if (density < (double)d.hScaled6) density = (double)d.hScaled6;
+    density *= d.massWpoly6;
+    const float rhoP = (float)density;
+    rho[d.N + id] = rhoP;
+    float p_corr = (rhoP - d.rho0) * d.delta;
+    if (p_corr < 0.f) p_corr = 0.f;
+    const float p = 0.f + p_corr;
+    pressure[id] = p;
+    recB[id] = f4(pi.x, pi.y, pi.z, p);
+    spPred[id] = piP;
   }
   const int base = (t & 31) - l;
   const float sx = __shfl_sync(0xffffffffu, s, base), sy = __shfl_sync(0xffffffffu, s, base + 1),
@@ -84,12 +111,9 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
     emask |= __shfl_xor_sync(0xffffffffu, emask, o);
   }
   if (!live || l != 0) return;
-  const float4 zero = f4(0.f, 0.f, 0.f, 0.f);
   if (!active) {  // boundary particle, as in k_forces
     acc[id] = zero;
     acc[d.N + id] = zero;
-    pressure[id] = 0.f;
-    spPred[id] = pi;
     return;
   }
   const float cv = d.massMu * (float)(d.del2W / (double)rho[id]);         // :688
@@ -98,10 +122,8 @@ __global__ void __launch_bounds__(LaneGeom<L>::T) k_forces_lanes(DevParams d, co
   a = a + f4(tx, ty, tz, 0.f);
   acc[id] = a;
   acc[d.N + id] = zero;
-  pressure[id] = 0.f;
   bMask[id] = bmask;
   if (elasticMask) elasticMask[id] = emask;
-  spPred[id] = predict_position(d, pi, vi, zero);
 }
 
 // predictDensity + correctPressure (k_predict_density<true, .>)
@@ -229,7 +251,7 @@ template <int L> static inline int lanes_grid(int n) { return (n + LaneGeom<L>::
 
 bool launch_forces_lanes(sph_ctx *c, int L) {
   float4 *pred = c->sortedPosition + c->d.N;
-#define F_ARGS c->d, c->sortedPosition, c->sortedVelocity, c->sortedType, c->nbIds, c->rho, c->acceleration, c->pressure, pred, c->recA, c->bMask, c->elasticMask
+#define F_ARGS c->d, c->sortedPosition, c->sortedVelocity, c->sortedType, c->nbIds, c->rho, c->acceleration, c->pressure, pred, c->recA, c->bMask, c->elasticMask, c->recB
   if (L == 4) launch_k(c, k_forces_lanes<4>, dim3(lanes_grid<4>(c->d.N)), dim3(LaneGeom<4>::T), F_ARGS);
   else if (L == 8) launch_k(c, k_forces_lanes<8>, dim3(lanes_grid<8>(c->d.N)), dim3(LaneGeom<8>::T), F_ARGS);
   else if (L == 16) launch_k(c, k_forces_lanes<16>, dim3(lanes_grid<16>(c->d.N)), dim3(LaneGeom<16>::T), F_ARGS);

@@ -27,6 +27,14 @@ __device__ __forceinline__ int search_cell(int cell, int off, int G) {
   return n;
 }
 
+// Cell id of a sorted particle (sortedPosition.w, sphFluid.cl:229). A particle that left the hash grid (NaN or a
+// position outside the box: cannot happen while integrate clamps positions) was binned into
+// the last cell by k_hash_count; the reference would index past gridCellIndex here — keep the loads in range instead.
+__device__ __forceinline__ int home_cell(const DevParams &d, float w) {
+  const int c = (int)w & d.mask;
+  return min(max(c, 0), d.G - 1);
+}
+
 // The 8 cells visited by a particle, in the reference's order (sphFluid.cl:248-308):
 // own, +x, +y, +z, +xy, +xz, +yz, +xyz with the per-axis direction chosen by which half of
 // its 2h cell the particle sits in (:253-271).
@@ -47,6 +55,9 @@ __device__ __forceinline__ void neighbor_cells(const DevParams &d, float4 pos, i
   cells[7] = search_cell(myCell, dx + dy + dz, d.G);
 }
 
+#ifndef SPH_SCAN_MAX_CELL
+#define SPH_SCAN_MAX_CELL 16384
+#endif
 // Generic path: one thread per particle, the reference's two passes. Used for cells the tiled kernel
 // cannot take (more candidate chunks than its mask table holds) and by the stage API.
 template <bool WITH_DENSITY>
@@ -54,14 +65,16 @@ __device__ __forceinline__ void find_neighbors_one(const DevParams &d, int id, c
                                                    const unsigned *__restrict__ cellStart, int *__restrict__ nb,
                                                    float *__restrict__ rho, float4 *__restrict__ recA = nullptr) {
   const float4 pos = sp[id];
-  const int myCell = (int)pos.w & d.mask;
+  const int myCell = home_cell(d, pos.w);
   int cells[8];
   neighbor_cells(d, pos, myCell, cells);
   int cb[8], ce[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) {
     cb[k] = (int)cellStart[cells[k]];
-    ce[k] = (int)cellStart[cells[k] + 1];
+    // a cell beyond SPH_SCAN_MAX_CELL particles exists only in a diverged simulation (see k_rank_reorder): its scan
+    // is cut so that a step stays finite
+    ce[k] = min((int)cellStart[cells[k] + 1], cb[k] + SPH_SCAN_MAX_CELL);
   }
   // pass 0: radial histogram of everything within h (sphFluid.cl:157-161). 30 bins x 6 bits in three 64-bit
   // registers, saturating at 63: the threshold rule below only asks whether a running sum is < 32, == 32 or > 32,
@@ -305,7 +318,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   }
   if (id >= d.N) return;
   const float4 pos = sp[id];
-  const int myCell = (int)pos.w & d.mask;
+  const int myCell = home_cell(d, pos.w);
   int cells[8];
   neighbor_cells(d, pos, myCell, cells);
   int cb[8], ce[8];
@@ -604,13 +617,16 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
 #ifndef SPH_COOP_MAX_N
 #define SPH_COOP_MAX_N (1 << 17)   // measured: config A (61 k) 0.088 -> 0.059 ms, config B (233 k) 0.136 -> 0.179 ms
 #endif
+#ifndef CP_MINB
+#define CP_MINB 3
+#endif
 #define CP_L 8
 #define CP_THREADS 256
 #define CP_P (CP_THREADS / CP_L)
 #define CP_CAP 128
 
 template <bool WITH_DENSITY>
-__global__ void __launch_bounds__(CP_THREADS, 3) k_find_neighbors_coop(DevParams d, const float4 *__restrict__ sp,
+__global__ void __launch_bounds__(CP_THREADS, CP_MINB) k_find_neighbors_coop(DevParams d, const float4 *__restrict__ sp,
                                                                     const float *__restrict__ S,
                                                                     const unsigned *__restrict__ cellStart,
                                                                     int *__restrict__ nb, float *__restrict__ rho,
@@ -624,7 +640,7 @@ __global__ void __launch_bounds__(CP_THREADS, 3) k_find_neighbors_coop(DevParams
   const bool live = id < d.N;
   const int gshift = (t & 31) - l;            // first lane of this particle's group inside the warp
   const float4 pos = sp[live ? id : 0];
-  const int myCell = (int)pos.w & d.mask;
+  const int myCell = home_cell(d, pos.w);
   int cells[8];
   neighbor_cells(d, pos, myCell, cells);
   int cb[8], ce[8], ng[8];                    // first / end index, number of aligned 16-groups per visited cell

@@ -16,6 +16,9 @@
 // position/velocity into sorted order. Nothing crosses PCIe.
 #include "sph_ctx.h"
 
+#ifndef SPH_RANK_MAX_CELL
+#define SPH_RANK_MAX_CELL 4096u
+#endif
 #define SCAN_THREADS 512
 #define SCAN_ITEMS 4
 #define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
@@ -48,6 +51,9 @@ __global__ void __launch_bounds__(256) k_hash_count(DevParams d, const float4 *_
   // The reference would index past gridCellIndex for a cell id >= G (cannot happen while
   // integrate clamps positions into the box); keep memory safe.
   unsigned bin = cell < (unsigned)d.G ? cell : (unsigned)d.G - 1u;
+  // particles outside the hash grid, or with a NaN coordinate ((int)NaN = 0: they land in cell 0), so far
+  // (sph_out_of_grid_count): the sign that a simulation has diverged
+  if (bin != cell || !(p.x == p.x) || !(p.y == p.y) || !(p.z == p.z)) atomicAdd(&nsStats[2], 1u);
   key[id] = cell;
   atomicAdd(&cellCount[bin], 1u);
 }
@@ -174,8 +180,13 @@ __global__ void __launch_bounds__(256) k_rank_reorder(DevParams d, const unsigne
   unsigned b = cellStart[bin], e = cellStart[bin + 1];
   unsigned rank = 0;
   // order within a cell = ascending original index (glibc's stable merge sort in _runSort); a slab rank
-  // ranks by GLOBAL id instead, which is the original index of the single-device run
-  if (rankKey) {  // rankKey = the keys in scatter order (tmpRankKey), contiguous per cell
+  // ranks by GLOBAL id instead, which is the original index of the single-device run.
+  // A cell with more than SPH_RANK_MAX_CELL particles (64x the rest density: only a diverged simulation, whose NaN
+  // and out-of-grid particles collapse into one cell, gets there) keeps the scatter order: the quadratic ranking of a
+  // million cell-mates would look like a hang, and there is no meaningful order left to preserve.
+  if (e - b > SPH_RANK_MAX_CELL) {
+    rank = (unsigned)s - b;
+  } else if (rankKey) {  // rankKey = the keys in scatter order (tmpRankKey), contiguous per cell
     const unsigned mine = rankKey[s];
     for (unsigned t = b; t < e; ++t) rank += (rankKey[t] < mine) ? 1u : 0u;
   } else {

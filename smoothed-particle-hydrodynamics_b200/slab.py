@@ -368,15 +368,31 @@ class PeerTransport:
 
     @classmethod
     def distributed(cls, rank_obj):
+        """Returns the transport, or None (on EVERY rank) when some rank could not map a neighbour's mailbox — e.g. a
+        process that sees only its own GPU: the caller then falls back to the NCCL protocol."""
         import torch.distributed as dist
         me, world = dist.get_rank(), dist.get_world_size()
         handles = [None] * world
-        dist.all_gather_object(handles, rank_obj.link_export())
-        if rank_obj.has[DOWN]:
-            rank_obj.link_open(DOWN, handles[me - 1])
-        if rank_obj.has[UP]:
-            rank_obj.link_open(UP, handles[me + 1])
-        dist.barrier()
+        ok = True
+        try:
+            mine = rank_obj.link_export()
+        except RuntimeError:
+            mine, ok = None, False
+        dist.all_gather_object(handles, mine)
+        if ok and all(h is not None for h in handles):
+            try:
+                if rank_obj.has[DOWN]:
+                    rank_obj.link_open(DOWN, handles[me - 1])
+                if rank_obj.has[UP]:
+                    rank_obj.link_open(UP, handles[me + 1])
+            except RuntimeError:
+                ok = False
+        else:
+            ok = False
+        flags = [None] * world
+        dist.all_gather_object(flags, ok)
+        if not all(flags):
+            return None
         return cls([rank_obj])
 
     def all_gather(self, rows):
