@@ -198,9 +198,11 @@ void owHelper::loadConfigurationToFile(float *position, float *connections, int 
 // ---- asynchronous recording: one writer thread, frames in call order ----
 namespace {
 struct RecJob { std::vector<float> position; float *connections; int *membranes; bool first; };
-std::mutex g_rec_mu;
-std::condition_variable g_rec_cv, g_rec_idle;
-std::deque<RecJob> g_rec_q;
+// heap objects that are never destroyed: the detached writer thread waits on them for the life of the process, and
+// destroying a condition variable with a waiter at exit (static destructors) blocks forever in pthread_cond_destroy
+std::mutex &g_rec_mu = *new std::mutex;
+std::condition_variable &g_rec_cv = *new std::condition_variable, &g_rec_idle = *new std::condition_variable;
+std::deque<RecJob> &g_rec_q = *new std::deque<RecJob>;
 bool g_rec_busy = false, g_rec_started = false;
 void rec_worker() {
   for (;;) {

@@ -65,6 +65,9 @@ void ow_helper_set_counts(int n, int ne, int nl, int nb, int nm) {
 void ow_helper_write_buffers(float *position, float *connections, int *membranes, int first) {
   owHelper::loadConfigurationToFile(position, connections, membranes, first != 0);
 }
+void ow_helper_write_buffers_async(float *position, float *connections, int *membranes, int first) {
+  owHelper::loadConfigurationToFileAsync(position, connections, membranes, first != 0);
+}
 // Reads frame `iteration`; on iteration 0 returns freshly allocated arrays through the out-pointers.
 int ow_helper_read_frame(float **position, float **connections, int **membranes, int iteration) {
   owHelper::loadConfigurationFromFile(*position, *connections, *membranes, iteration);

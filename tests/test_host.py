@@ -413,3 +413,35 @@ def test_simulator_config_bprime_from_files(tmp_path):
     assert common.first_mismatch(v, o.read("velocity", len(pos))) is None
     L.ow_sim_destroy(sim)
     o.close()
+
+
+def test_async_recording_writes_in_order_and_the_process_exits(tmp_path):
+    """-l_to frames are formatted by a writer thread (owHelper::loadConfigurationToFileAsync). In a process of its own:
+    three frames queued back to back arrive in order, flushRecording waits for them, and the process EXITS (a writer
+    thread waiting on a condition variable that static destructors tear down would hang it)."""
+    import subprocess
+    import textwrap
+    code = textwrap.dedent('''
+        import ctypes as C, numpy as np, sys
+        L = C.CDLL(sys.argv[1])
+        L.ow_set_buffers_dir.argtypes = [C.c_char_p]
+        L.ow_set_buffers_dir(sys.argv[2].encode())
+        n = 5000
+        L.ow_helper_set_counts(n, 0, n, 0, 0)
+        L.ow_helper_write_buffers_async.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        p = np.zeros((n, 4), np.float32); p[:, 3] = 1.1
+        for f in range(3):
+            p[:, 0] = f + 1          # the frame is copied at the call: changing p afterwards must not matter
+            L.ow_helper_write_buffers_async(p.ctypes.data_as(C.c_void_p), None, None, 1 if f == 0 else 0)
+        p[:, 0] = 99
+        L.ow_flush_recording()
+        rows = np.loadtxt(sys.argv[2] + "/position_buffer.txt", skiprows=2)
+        assert rows.shape == (3 * n, 4), rows.shape
+        assert (rows[:n, 0] == 1).all() and (rows[n:2 * n, 0] == 2).all() and (rows[2 * n:, 0] == 3).all()
+        print("frames ok", flush=True)
+        ''')
+    b = importlib.import_module(common.PKG + ".build")
+    lib = b.build_host()
+    (tmp_path / "buffers").mkdir()
+    r = subprocess.run([sys.executable, "-c", code, lib, str(tmp_path / "buffers")], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "frames ok" in r.stdout, r.stdout + r.stderr[-2000:]
