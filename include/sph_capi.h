@@ -201,6 +201,9 @@ int sph_profile_enable(sph_ctx *ctx, int on);
 int sph_profile_report(sph_ctx *ctx, char *buf, size_t n);
 /* Number of kernels sph_step has launched on this context. */
 long long sph_launch_count(const sph_ctx *ctx);
+/* Tuning counters of the neighbour search: {needy particles of the last search, its histogram-first mode, out-of-grid /
+ * NaN particles so far, fallbacks to the plain scan so far}. Synchronises. */
+int sph_debug_counters(sph_ctx *ctx, unsigned out[4]);
 /* Particles found outside the hash grid so far (NaN / out-of-box positions; 0 in a healthy run). Synchronises. */
 long long sph_out_of_grid_count(sph_ctx *ctx);
 /* Page-locked host memory for read-back / upload buffers. */

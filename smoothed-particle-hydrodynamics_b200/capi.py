@@ -224,6 +224,11 @@ class SphContext:
         self.L.check(self.L.lib.sph_empty_chain_ms(self.h, int(nodes), int(blocks), int(threads), int(replays), C.byref(ms)), "sph_empty_chain_ms")
         return float(ms.value)
 
+    def debug_counters(self):
+        out = (C.c_uint * 4)()
+        self.L.check(self.L.lib.sph_debug_counters(self.h, out), "sph_debug_counters")
+        return list(out)
+
     def out_of_grid_count(self):
         return int(self.L.lib.sph_out_of_grid_count(self.h))
 

@@ -697,6 +697,16 @@ int sph_timer_stop(sph_ctx *c, float *elapsed_ms) {
 
 long long sph_launch_count(const sph_ctx *c) { return c ? c->launches : 0; }
 
+// {particles that needed the radial histogram in the last neighbour search, histogram-first mode of that search,
+//  out-of-grid / NaN particles so far, particles that fell back to the plain two-pass scan so far}. Synchronises.
+int sph_debug_counters(sph_ctx *c, unsigned out[4]) {
+  if (!c || !out) return fail(SPH_E_INVALID, "sph_debug_counters");
+  CU(cudaSetDevice(c->device));
+  CU(cudaStreamSynchronize(c->stream));
+  CU(cudaMemcpy(out, c->nsStats, 16, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
 // Particles that the hash found outside the grid or with a NaN coordinate since the context was created;
 // they are binned into the last cell, where a crowd of them makes the in-cell ranking quadratic. Synchronises.
 long long sph_out_of_grid_count(sph_ctx *c) {

@@ -465,6 +465,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     }
   }
   if (!fits || n > LP_CAP + LP_OVF || ne > LP_ECAP + LP_EOVF) {
+    if (nsStats) atomicAdd(&nsStats[3], 1u);   // particles that took the plain two-pass scan so far (sph_debug_counters)
     find_neighbors_one<WITH_DENSITY>(d, id, sp, cellStart, nb, rho, recA);
     return;
   }

@@ -15,9 +15,12 @@ while done < before:
         print("diverged after", done); sys.exit(1)
 import numpy as np
 print("pressure>0 frac", float((ctx.read("pressure") > 0).mean()), "after", done, "steps")
+c0 = ctx.debug_counters()
 ctx.profile(True)
 ms = ctx.run_steps(30) / 30
 pr = ctx.profile_report()
 print(name, "ms/step %.4f" % ms, {k: round(v["ms"] / 30, 4) for k, v in pr.items()})
+c1 = ctx.debug_counters()
+print("counters: needy last search %d (%.1f%%), hist-first mode %d, fallbacks to the plain scan per step %.0f (%.2f%%)" % (c1[0], 100.0 * c1[0] / len(pos), c1[1], (c1[3] - c0[3]) / 30.0, 100.0 * (c1[3] - c0[3]) / 30.0 / len(pos)))
 nm = ctx.read("neighborMap")
 print("mean neighbours", float((nm[:, 0] >= 0).reshape(-1, 32).sum(1).mean()))
