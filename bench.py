@@ -221,6 +221,7 @@ def run_reference(args, rank):
 # ---------------------------------------------------------------- the drop-in C++ class (libow_b200.so)
 _FACADE = None
 TRANSPORT_USED = None
+E2E_BYTES = 16
 LAST_CHAIN_FLOOR_MS = None   # dependent chain of as many EMPTY kernels as the last timed step had (small scenes)
 
 
@@ -394,6 +395,8 @@ def time_slab(slab, torch, dist, L, r, tr, warmup, steps, e2e=True):
         r._check(r.lib.sph_slab_read_owned(r.ctx.h, host_pos[0].ctypes.data_as(C.c_void_p), None, None), "read_owned")
 
     marks = []
+    xyz = os.environ.get("SPH_E2E_XYZ", "1") != "0" and hasattr(L.lib, "sph_slab_read_owned_xyz_begin")
+    out["e2e_bytes_per_particle"] = 12 if xyz else 16
 
     def pipelined(s):
         t = [time.perf_counter()]
@@ -406,7 +409,13 @@ def time_slab(slab, torch, dist, L, r, tr, warmup, steps, e2e=True):
         else:
             slab.slab_step(tr); t.append(time.perf_counter())
         r.ctx.read_end(); t.append(time.perf_counter())
-        r.read_owned_begin(host_pos[s & 1]); t.append(time.perf_counter())
+        if xyz:   # packed (x, y, z): 12 bytes per particle; the ids are fetched again only when particles migrated
+            if linked and (r.counts[0] or r.counts[2]):
+                r.read_gid()
+            r.read_owned_xyz_begin(host_pos[s & 1])
+        else:
+            r.read_owned_begin(host_pos[s & 1])
+        t.append(time.perf_counter())
         marks.append([round((b - a) * 1e3, 2) for a, b in zip(t, t[1:])])
 
     blocking(0)
@@ -629,6 +638,8 @@ def main():
             total = int(cnt[0])
             slab_info = dict(n_local=info[1], halo=info[2:6], z=[sc["z0"], sc["z1"]], n_total=sc["n_total"])
             prof, launches, e2e_steps = res["prof"], res["launches"], res["e2e_steps"]
+            global E2E_BYTES
+            E2E_BYTES = res["e2e_bytes_per_particle"]
             del sc
             if not args.no_configs:   # BASELINE config D: ONE 16 M fluid divided among the ranks
                 sc = scenes.slab_scene("fluid_16m", world, rank, stack=1)
@@ -648,7 +659,10 @@ def main():
                                        "n1_ms_per_step": n1[0], "efficiency_vs_n1": n1[0] / (float(t[0]) * world),
                                        "limiter": "halo exchange latency + ghost layers: the per-step exchange cost does "
                                                   "not shrink with the slab while the kernels do"}
-        e2e_mode = "slab ranks: muscle signal up, step, owned positions back (pinned), pipelined with the next step"
+        e2e_mode = ("slab ranks: muscle signal up, step, owned positions back into pinned host memory every step, pipelined "
+                    "with the next step; %d bytes per particle (%s)" %
+                    (E2E_BYTES, "packed x, y, z: the type tag is constant; ids re-read only after a migration" if E2E_BYTES == 12
+                     else "x, y, z, type"))
     else:
         dist = None
         scene = make_workload(args.workload, L)
@@ -688,7 +702,7 @@ def main():
                        (world, TRANSPORT_USED)},
             "clocks": clocks,
             "e2e": {"value": total / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 400,
-                    "d2h_bytes_per_step": 16 * n, "ms_per_step": e2e_ms, "steps": e2e_steps, "mode": e2e_mode,
+                    "d2h_bytes_per_step": E2E_BYTES * n, "ms_per_step": e2e_ms, "steps": e2e_steps, "mode": e2e_mode,
                     "blocking_value": total / (e2e_blocking_ms * 1e-3), "blocking_ms_per_step": e2e_blocking_ms},
             "gpu_launches": launches, "roofline": roof}
     if world == 1:

@@ -243,6 +243,9 @@ int sph_slab_read_owned(sph_ctx *ctx, float *pos4, float *vel4, uint32_t *gid);
 int sph_slab_set_cut(sph_ctx *ctx, int z0, int z1);
 /* Pipelined form for the owned positions (pinned pos4): overlaps the next step; complete it with sph_read_end. */
 int sph_slab_read_owned_begin(sph_ctx *ctx, float *pos4);
+/* The same for packed (x, y, z) — 12 bytes per particle: the type tag never changes. Local order; it changes only in
+ * steps that migrate particles (sph_slab_counts), sph_slab_read_owned(ctx, NULL, NULL, gid) gives the ids then. */
+int sph_slab_read_owned_xyz_begin(sph_ctx *ctx, float *xyz3);
 const char *sph_slab_last_error(void);
 /* ---- links: halo exchange through PEER MEMORY (NVLink / NVSwitch P2P; north_star: "ghost-particle halos exchanged
  * by NCCL (or P2P) over NVLink each step"). Every rank owns a mailbox in device memory that its two neighbours map

@@ -842,6 +842,7 @@ int sph_read_end(sph_ctx *c) {
   CU(cudaSetDevice(c->device));
   CU(cudaEventSynchronize(c->evReadDone));
   c->readPending = 0;
+  c->readStaged = false;
   return 0;
 }
 

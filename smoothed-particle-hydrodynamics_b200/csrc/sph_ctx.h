@@ -93,6 +93,7 @@ struct sph_ctx {
   cudaEvent_t evReadReady, evReadDone;
   int readPending;
   const void *readSrc;         // device buffer the pending read copies from
+  bool readStaged;             // the pending read copies from a staging buffer: writers of position / velocity need not wait
   float *snapRho;              // sph_snapshot: rho(t) and particleIndex of the last completed step
   uint2 *snapIndex;
   float4 *snapVel;             // only when the caller asked for it
@@ -126,7 +127,7 @@ static inline void launch_k(sph_ctx *c, void (*kernel)(KArgs...), dim3 grid, dim
 
 // order the next writer of position / velocity after a pending pipelined read of them
 static inline void read_fence(sph_ctx *c) {
-  if (c->readPending && !c->capturing) cudaStreamWaitEvent(c->stream, c->evReadDone, 0);
+  if (c->readPending && !c->capturing && !c->readStaged) cudaStreamWaitEvent(c->stream, c->evReadDone, 0);
 }
 
 // per-kernel event timing (sph_profile_enable) for the slab kernels; defined in sph_capi.cu

@@ -96,6 +96,8 @@ class SlabRank:
         L.sph_slab_unpack.argtypes = [V, I, I, V]
         L.sph_slab_read_owned.argtypes = [V, V, V, V]
         L.sph_slab_read_owned_begin.argtypes = [V, V]
+        if hasattr(L, "sph_slab_read_owned_xyz_begin"):
+            L.sph_slab_read_owned_xyz_begin.argtypes = [V, V]
         L.sph_slab_set_cut.argtypes = [V, I, I]
         L.sph_slab_last_error.restype = C.c_char_p
         L.sph_step_part.argtypes = [V, I]
@@ -185,6 +187,17 @@ class SlabRank:
         """Pipelined read of the owned positions into `out` (pinned, >= n_owned rows); finish with ctx.read_end()."""
         self._check(self.lib.sph_slab_read_owned_begin(self.ctx.h, out.ctypes.data_as(C.c_void_p)),
                     "sph_slab_read_owned_begin")
+
+    def read_owned_xyz_begin(self, out):
+        """Pipelined read of the owned positions as packed (x, y, z) into `out` (pinned, >= 3 * n_owned floats)."""
+        self._check(self.lib.sph_slab_read_owned_xyz_begin(self.ctx.h, out.ctypes.data_as(C.c_void_p)),
+                    "sph_slab_read_owned_xyz_begin")
+
+    def read_gid(self):
+        n = self.info()[0]
+        gid = np.empty(n, np.uint32)
+        self._check(self.lib.sph_slab_read_owned(self.ctx.h, None, None, gid.ctypes.data_as(C.c_void_p)), "sph_slab_read_owned")
+        return gid
 
     def close(self):
         self.ctx.close()

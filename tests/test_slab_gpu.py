@@ -88,6 +88,10 @@ def run_slabs(P, p, pos, vel, world, steps):
         r.read_owned_begin(buf)
         r.ctx.read_end()
         assert np.array_equal(buf[:len(want)], want)
+        xyz = P.pinned_array((3 * (len(want) + 8),))   # and the packed (x, y, z) form
+        r.read_owned_xyz_begin(xyz)
+        r.ctx.read_end()
+        assert np.array_equal(xyz[:3 * len(want)].reshape(-1, 3), want[:, :3])
     out = slab.gather_owned(ranks, len(pos))
     infos = [r.info() for r in ranks]
     for r in ranks:
