@@ -395,7 +395,10 @@ def time_slab(slab, torch, dist, L, r, tr, warmup, steps, e2e=True):
         r._check(r.lib.sph_slab_read_owned(r.ctx.h, host_pos[0].ctypes.data_as(C.c_void_p), None, None), "read_owned")
 
     marks = []
-    xyz = os.environ.get("SPH_E2E_XYZ", "1") != "0" and hasattr(L.lib, "sph_slab_read_owned_xyz_begin")
+    # SPH_E2E_XYZ=1: packed (x, y, z), 12 bytes per particle. Off by default: the local order changes with every
+    # migration (a few particles cross a cell layer in almost every step even of a fluid at rest), so a consumer needs
+    # the ids again each time — measured at 4 GPUs: 3.96 G with 16-byte rows, 2.70 G with packed rows + a blocking id read
+    xyz = os.environ.get("SPH_E2E_XYZ", "0") == "1" and hasattr(L.lib, "sph_slab_read_owned_xyz_begin")
     out["e2e_bytes_per_particle"] = 12 if xyz else 16
 
     def pipelined(s):
