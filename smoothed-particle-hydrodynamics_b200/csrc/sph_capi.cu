@@ -268,7 +268,9 @@ sph_ctx *sph_create(const sph_params *p, const float *pos4, const float *vel4, c
     const char *ln = getenv("SPH_LANES");
     c->lanes = ln ? atoi(ln) : 0;
     const char *hp = getenv("SPH_HIST_PCT");
-    c->hist_pct = hp ? (unsigned)atoi(hp) : 5u;
+    c->hist_pct = (hp ? (unsigned)atoi(hp) : 5u) & 255u;
+    const char *hp2 = getenv("SPH_HIST2_PCT");  // histogram-ONLY first pass above this share of needy particles
+    c->hist_pct |= ((hp2 ? (unsigned)atoi(hp2) : 30u) & 255u) << 8;
     const char *pd = getenv("SPH_PDL");
     c->pdl_mode = pd ? atoi(pd) : -1;
   }

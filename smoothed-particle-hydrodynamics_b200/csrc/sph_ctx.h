@@ -63,7 +63,7 @@ struct sph_ctx {
   float2 *nmScratch;           // 32N float2, lazily allocated for sph_read(NEIGHBOR_MAP)
   float4 *readScratch;
   unsigned *elasticMask;       // N words, scenes with membranes only: bit k = neighbour slot k holds an elastic particle
-  unsigned hist_pct;           // SPH_HIST_PCT (see k_hash_count)
+  unsigned hist_pct;           // SPH_HIST_PCT (bits 0-7) and SPH_HIST2_PCT (bits 8-15), see k_hash_count
   unsigned *nsStats;           // [0] particles that needed the radial histogram this step, [1] this step's mode (k_hash_count)
   int *memList, *memCount;     // scenes with membranes: sorted ids of the liquid particles with an elastic neighbour (this step)
   bool has_elastic, has_membranes, has_pml;

@@ -517,6 +517,10 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   // The choice is made per STEP for all threads alike (a per-thread choice diverges inside the warps and costs both):
   // nsStats[1], set by k_hash_count from the number of particles that needed the histogram in the previous step.
   const bool histFirst = VAR != 2 || nsStats == nullptr || nsStats[1] != 0u;
+  // third mode (nsStats[1] == 2, more than SPH_HIST2_PCT % needy): the first pass only builds the histogram and EVERY
+  // particle selects in the second pass — the speculative selection (store, sqrt, fp64 add per hit) would be thrown
+  // away by most of them
+  const bool histOnly = VAR == 2 && nsStats != nullptr && nsStats[1] == 2u;
   int within = 0;
   // HIST is a compile-time constant per call site: the loop without the histogram must not keep its four 64-bit
   // accumulators alive (a run-time flag inside one loop cost 0.3 ms at 8 M particles)
@@ -546,7 +550,14 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     return (curCode + (unsigned)i) & 0xffffu;
   };
   if (VAR == 2) {
-    if (histFirst) { for (int t = 0; t < n; t++) first_pass(next_hit(), LpYes()); }
+    if (histOnly) {  // most particles will select again with a smaller r_thr: no speculative selection at all
+      for (int t = 0; t < n; t++) {
+        const int j = hit_index(next_hit());
+        if (j == id) continue;
+        const float dd = dist2(j);
+        if (dd <= h2) { within++; hist_add(dd); }
+      }
+    } else if (histFirst) { for (int t = 0; t < n; t++) first_pass(next_hit(), LpYes()); }
     else { for (int t = 0; t < n; t++) first_pass(next_hit(), LpNo()); }
     if (!histFirst && within >= SPH_NB) {   // the histogram decides r_thr after all: build it
       curMask = 0u;
@@ -574,7 +585,8 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
       if (open && sum >= SPH_NB) { jthr = (sum == SPH_NB) ? jj : jj - 1; open = false; }
     }
   }
-  if (jthr != SPH_RADIUS_SEGMENTS) {  // a smaller r_thr: select again
+  if (jthr != SPH_RADIUS_SEGMENTS || histOnly) {  // a smaller r_thr: select again (histOnly: select at all;
+                                                  // jthr == SEGMENTS gives r2 == r2open, the same expression)
     const float r_thr = (float)(jthr + 1) * d.h / SPH_RADIUS_SEGMENTS;
     const float r2 = r_thr * r_thr;
     found = 0;

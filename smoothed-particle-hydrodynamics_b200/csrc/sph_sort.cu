@@ -35,7 +35,12 @@ __global__ void __launch_bounds__(256) k_hash_count(DevParams d, const float4 *_
   int id = blockIdx.x * blockDim.x + threadIdx.x;
   // neighbour search of this step: histogram in the first pass if more than histPct % of the particles needed it in
   // the previous step (see k_find_neighbors_list); then restart the count
-  if (id == 0) { nsStats[1] = (100ull * nsStats[0] > (unsigned long long)histPct * (unsigned long long)d.N) ? 1u : 0u; nsStats[0] = 0u; }
+  // (histPct bits 0-7); above the percentage in bits 8-15 the first pass builds the histogram only (mode 2)
+  if (id == 0) {
+    const unsigned long long needy = 100ull * nsStats[0], n = (unsigned long long)d.N;
+    nsStats[1] = (needy > (unsigned long long)(histPct >> 8) * n) ? 2u : (needy > (unsigned long long)(histPct & 255u) * n) ? 1u : 0u;
+    nsStats[0] = 0u;
+  }
   // reset the look-back scan of this step's sort (k_scan_cells runs after this kernel): the step's launch
   // parameters are then the same every step, which is what lets sph_step replay a captured CUDA graph
   for (int t = id; t < scanTiles; t += gridDim.x * blockDim.x) scanState[t] = 0ull;

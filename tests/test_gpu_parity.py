@@ -42,7 +42,8 @@ STAGE_OUTPUTS = {
 VARIANTS = {
     "tiles": dict(SPH_NEIGHBOR_PATH="tiles", SPH_LANES="1", SPH_GRAPH="0", SPH_PDL="0"),
     "generic-lanes4-pdl": dict(SPH_NEIGHBOR_PATH="generic", SPH_LANES="4", SPH_GRAPH="0", SPH_PDL="1"),
-    "list-lanes16-graph": dict(SPH_NEIGHBOR_PATH="list", SPH_LANES="16", SPH_GRAPH="1", SPH_PDL="0"),
+    "list-histonly-lanes16-graph": dict(SPH_NEIGHBOR_PATH="list", SPH_LANES="16", SPH_GRAPH="1", SPH_PDL="0",
+                                        SPH_HIST2_PCT="0"),   # histogram-only first pass from the second step on
     "coop-lanes8-graph-pdl": dict(SPH_NEIGHBOR_PATH="coop", SPH_LANES="8", SPH_GRAPH="1", SPH_PDL="1"),
     "default": dict(),   # what the library picks by size: the product path
 }
@@ -53,7 +54,7 @@ def neighbor_path(request):
     """Force the independent implementations of the step's kernels through their environment switches (read at
     sph_create): the tile / plain / list / cooperative neighbour search, 1 / 4 / 8 / 16 lanes per particle in the
     gather kernels, eager launches or the captured CUDA graph, plain or programmatic dependent launches."""
-    keys = ["SPH_NEIGHBOR_PATH", "SPH_LANES", "SPH_GRAPH", "SPH_PDL"]
+    keys = ["SPH_NEIGHBOR_PATH", "SPH_LANES", "SPH_GRAPH", "SPH_PDL", "SPH_HIST2_PCT"]
     old = {k: os.environ.get(k) for k in keys}
     for k in keys:
         os.environ.pop(k, None)
