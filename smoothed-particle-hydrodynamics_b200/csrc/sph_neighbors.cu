@@ -209,11 +209,17 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #endif
 // VAR 2 keeps one 32-bit ENTRY per non-empty group of 16 candidates instead of one 16-bit code per hit:
 // (code of the group's first candidate) << 16 | 16-bit hit mask. ~25 entries per particle on the lattice fluid.
+// Shared memory is what limits the kernel to 10 CTAs per SM (20 624 bytes each: one more row of entries and only 9
+// fit, measured 2.69 -> 2.75 ms): 28 rows of entries + the 8 rows of cell bases (cbS) measured faster than 36 rows of
+// entries with the bases in local memory (2.75 -> 2.69 ms; 26 / 27 / 28 rows: 2.71 / 2.69 / 2.69 ms).
 #ifndef LP_ECAP
-#define LP_ECAP 36
+#define LP_ECAP 28
 #endif
 #ifndef LP_EOVF
-#define LP_EOVF 28
+#define LP_EOVF 36
+#endif
+#ifndef SPH_LP_CBS
+#define SPH_LP_CBS 1
 #endif
 
 
@@ -276,6 +282,12 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   __shared__ int binCount[64], binBase[64];
   __shared__ int binTot0;
   __shared__ unsigned char srcOf[LP_THREADS];
+#if SPH_LP_CBS
+  // first index of the 8 visited cells, one column per thread: the select phase looks it up by a run-time cell number
+  // for every entry — from a per-thread local array that was 7 L1 sectors per warp access (lanes differ in the cell
+  // they are at: 16 of the kernel's 59 L1 sectors per particle, ncu source view), from here it is one wavefront
+  __shared__ int cbS[8][LP_THREADS];
+#endif
   pdl_entry();
   const int tid = threadIdx.x;
   // Lanes that share (cell, octant) walk the same cells in lockstep and load the same addresses. The CTA's 128
@@ -328,6 +340,9 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     cb[k] = (int)cellStart[cells[k]];
     ce[k] = (int)cellStart[cells[k] + 1];
     fits = fits && (ce[k] - cb[k] < 8192);
+#if SPH_LP_CBS
+    cbS[k][tid] = cb[k];
+#endif
   }
   const float rmaxf = (float)(SPH_RADIUS_SEGMENTS + 1) * d.h / SPH_RADIUS_SEGMENTS;  // largest r_thr (j == 30)
   const float rfilt2 = rmaxf * rmaxf * 1.0001f;
@@ -470,7 +485,11 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     return;
   }
   // exact distances of the hits (the particle itself is among them: skipped by index)
+#if SPH_LP_CBS
+  auto hit_index = [&](unsigned hv) { return cbS[hv >> 13][tid] + (int)(hv & 8191u); };
+#else
   auto hit_index = [&](unsigned hv) { return cb[hv >> 13] + (int)(hv & 8191u); };
+#endif
   auto dist2 = [&](int j) {
     const float4 q = ldg4(sp + j);
     const float ex = pos.x - q.x, ey = pos.y - q.y, ez = pos.z - q.z;
@@ -524,8 +543,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   int within = 0;
   // HIST is a compile-time constant per call site: the loop without the histogram must not keep its four 64-bit
   // accumulators alive (a run-time flag inside one loop cost 0.3 ms at 8 M particles)
-  auto first_pass = [&](unsigned hv, auto HIST) {
-    const int j = hit_index(hv);
+  auto first_pass = [&](int j, auto HIST) {
     if (j == id) return;
     const float dd = dist2(j);
     if (dd <= h2) {
@@ -536,23 +554,26 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   };
   // VAR 2: walk the hits of the entry list in scan order — a flat loop over the n hits (one per iteration for every
   // lane), fetching the next entry whenever the current mask is used up (entries are never empty)
-  unsigned curMask = 0u, curCode = 0u;
-  int curEntry = 0;
-  auto next_hit = [&]() -> unsigned {
+  // The sorted index of candidate i of an entry is (index of its first hit) + (i - i0): the cell number is decoded
+  // once per entry, from the code of its first HIT (the group's first candidate may lie in the cell before).
+  unsigned curMask = 0u;
+  int curBase = 0, curEntry = 0;
+  auto next_hit = [&]() -> int {
     if (curMask == 0u) {
       const unsigned e = (curEntry < LP_ECAP) ? ent[curEntry][tid] : ovfE[min(curEntry - LP_ECAP, LP_EOVF - 1)];
       curEntry++;
       curMask = e & 0xffffu;
-      curCode = e >> 16;
+      const int i0 = __ffs(curMask) - 1;
+      curBase = hit_index(((e >> 16) + (unsigned)i0) & 0xffffu) - i0;
     }
     const int i = __ffs(curMask) - 1;
     curMask &= curMask - 1u;
-    return (curCode + (unsigned)i) & 0xffffu;
+    return curBase + i;
   };
   if (VAR == 2) {
     if (histOnly) {  // most particles will select again with a smaller r_thr: no speculative selection at all
       for (int t = 0; t < n; t++) {
-        const int j = hit_index(next_hit());
+        const int j = next_hit();
         if (j == id) continue;
         const float dd = dist2(j);
         if (dd <= h2) { within++; hist_add(dd); }
@@ -563,7 +584,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
       curMask = 0u;
       curEntry = 0;
       for (int t = 0; t < n; t++) {
-        const int j = hit_index(next_hit());
+        const int j = next_hit();
         if (j == id) continue;
         const float dd = dist2(j);
         if (dd <= h2) hist_add(dd);
@@ -571,8 +592,8 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     }
   } else {
     const int nList = min(n, LP_CAP);
-    for (int t = 0; t < nList; t++) first_pass(hits[t][tid], LpYes());
-    for (int t = LP_CAP; t < n; t++) first_pass(ovf[t - LP_CAP], LpYes());
+    for (int t = 0; t < nList; t++) first_pass(hit_index(hits[t][tid]), LpYes());
+    for (int t = LP_CAP; t < n; t++) first_pass(hit_index(ovf[t - LP_CAP]), LpYes());
   }
   int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
   {
@@ -594,7 +615,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     curMask = 0u;
     curEntry = 0;
     for (int t = 0; t < n && found < SPH_NB; t++) {
-      const int j = hit_index(VAR == 2 ? next_hit() : (unsigned)((t < LP_CAP) ? hits[t][tid] : ovf[t - LP_CAP]));
+      const int j = VAR == 2 ? next_hit() : hit_index((unsigned)((t < LP_CAP) ? hits[t][tid] : ovf[t - LP_CAP]));
       if (j == id) continue;
       const float dd = dist2(j);
       if (dd <= r2) take(j, dd);
