@@ -2,7 +2,7 @@
 # usage: tools/gpu_scale.sh N   — bench.py on N GPUs (weak fluid_8m per GPU + strong fluid_16m + slab parity self-check)
 N=$1
 mkdir -p gpurun_out
-SPH_BENCH_MARKS=1 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/r02_bench_n$N.json 2> gpurun_out/r02_bench_n$N.err; echo "n$N rc=$?"
+SPH_BENCH_MARKS=1 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/r02_bench_n$N.json 2> gpurun_out/r02_bench_n$N.err; echo "n$N rc=$?"
 grep -v "^\*\*\*\|OMP_NUM" gpurun_out/r02_bench_n$N.err | tail -12
 python - <<P
 import json
