@@ -221,6 +221,9 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #ifndef SPH_LP_CBS
 #define SPH_LP_CBS 1
 #endif
+#ifndef SPH_LP_PRMT
+#define SPH_LP_PRMT 1
+#endif
 
 
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
@@ -377,18 +380,40 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
         ld256u(g, xa, xb);
         ld256u(g + 16, ya, yb);
         ld256u(g + 32, za, zb);
-        unsigned m = 0u;  // bit r = candidate j + r, bit 16 + r = candidate j + 8 + r (r < 8): inside the filter
-        auto lane2 = [&](unsigned x, unsigned y, unsigned z, int r) {
+        unsigned m = 0u;
+        auto dist2T = [&](unsigned x, unsigned y, unsigned z) {  // (d2 - T) of candidates r (low half) and 8 + r (high)
           const __half2 ex = __hsub2(*reinterpret_cast<const __half2 *>(&x), px);
           const __half2 ey = __hsub2(*reinterpret_cast<const __half2 *>(&y), py);
           const __half2 ez = __hsub2(*reinterpret_cast<const __half2 *>(&z), pz);
-          const __half2 a = __hfma2(ez, ez, __hfma2(ey, ey, __hfma2(ex, ex, nT)));  // d2 - T: negative = hit
-          m |= ((*reinterpret_cast<const unsigned *>(&a)) >> (15 - r)) & (0x00010001u << r);
+          const __half2 a = __hfma2(ez, ez, __hfma2(ey, ey, __hfma2(ex, ex, nT)));  // negative = hit
+          return *reinterpret_cast<const unsigned *>(&a);
+        };
+#if SPH_LP_PRMT
+        // The four sign bits of two such words (candidates r, 8 + r, r + 4, 12 + r) are turned into four byte masks
+        // by ONE byte permute with sign replication (selector nibbles 9, B, D, F: the sign of bytes 1 and 3 of either
+        // operand) and placed by ONE and-or: 2 instructions per 4 candidates instead of 4 (shift + and-or per pair).
+        auto quad = [&](unsigned a, unsigned b, int r) {
+          unsigned w;
+          asm("prmt.b32 %0, %1, %2, 0xFDB9;" : "=r"(w) : "r"(a), "r"(b));
+          m |= w & (0x10100101u << r);  // bits r | 8 + r | 20 + r | 28 + r
+        };
+        quad(dist2T(xa.x, ya.x, za.x), dist2T(xb.x, yb.x, zb.x), 0);
+        quad(dist2T(xa.y, ya.y, za.y), dist2T(xb.y, yb.y, zb.y), 1);
+        quad(dist2T(xa.z, ya.z, za.z), dist2T(xb.z, yb.z, zb.z), 2);
+        quad(dist2T(xa.w, ya.w, za.w), dist2T(xb.w, yb.w, zb.w), 3);
+        // fold to 16 ascending bits (bit i = candidate j + i); the group is aligned to 16: its ends may reach into the
+        // neighbouring cells
+        m = (m | (m >> 16)) & 0xffffu;
+#else
+        // bit r = candidate j + r, bit 16 + r = candidate j + 8 + r (r < 8): inside the filter
+        auto lane2 = [&](unsigned x, unsigned y, unsigned z, int r) {
+          m |= (dist2T(x, y, z) >> (15 - r)) & (0x00010001u << r);
         };
         lane2(xa.x, ya.x, za.x, 0); lane2(xa.y, ya.y, za.y, 1); lane2(xa.z, ya.z, za.z, 2); lane2(xa.w, ya.w, za.w, 3);
         lane2(xb.x, yb.x, zb.x, 4); lane2(xb.y, yb.y, zb.y, 5); lane2(xb.z, yb.z, zb.z, 6); lane2(xb.w, yb.w, zb.w, 7);
         // fold to 16 ascending bits; the group is aligned to 16: its ends may reach into the neighbouring cells
         m = (m & 0xffu) | ((m >> 8) & 0xff00u);
+#endif
         m &= (0xffffu << max(b - j, 0)) & (0xffffu >> max(j + 16 - e, 0));
         // One entry per non-empty group; the hits are unpacked by the select phase, whose loop runs at nearly full
         // lane occupancy. (Appending hit by hit here cost 27 % of the kernel's instructions at 6 active lanes of 32:
