@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #define LP_OVF 72
 #endif
 // VAR 2 keeps one 32-bit ENTRY per non-empty group of 16 candidates instead of one 16-bit code per hit:
-// (code of the group's first candidate) << 16 | 16-bit hit mask. ~25 entries per particle on the lattice fluid.
+// (cell number k << 13 | rank of the group's first candidate in the cell + 16) << 16 | 16-bit hit mask. ~25 entries per particle on the lattice fluid.
 // Shared memory is what limits the kernel to 10 CTAs per SM (20 624 bytes each: one more row of entries and only 9
 // fit, measured 2.69 -> 2.75 ms): 28 rows of entries + the 8 rows of cell bases (cbS) measured faster than 36 rows of
 // entries with the bases in local memory (2.75 -> 2.69 ms; 26 / 27 / 28 rows: 2.71 / 2.69 / 2.69 ms).
@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   for (int k = 0; k < 8; k++) {
     cb[k] = (int)cellStart[cells[k]];
     ce[k] = (int)cellStart[cells[k] + 1];
-    fits = fits && (ce[k] - cb[k] < 8192);
+    fits = fits && (ce[k] - cb[k] < 8176);  // 13-bit ranks, biased by 16 in the entries of VAR 2
 #if SPH_LP_CBS
     cbS[k][tid] = cb[k];
 #endif
@@ -369,7 +369,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
 #pragma unroll 1
     for (int k = 0; k < 8; k++) {
       const int b = cb[k], e = ce[k];
-      const int enc = (k << 13) - b - 1;  // hit = enc + j + candidate + 1 = (k << 13) | rank in cell
+      const int enc = (k << 13) - b + 16;  // entry code of group j = (k << 13) | (j - b + 16): the aligned group may start up to 15 before the cell
       const __half2 px = __float2half2_rn(up.x - (((0xB2 >> k) & 1) ? sgx : 0.0f));
       const __half2 py = __float2half2_rn(up.y - (((0xD4 >> k) & 1) ? sgy : 0.0f));
       const __half2 pz = __float2half2_rn(up.z - (((0xE8 >> k) & 1) ? sgz : 0.0f));
@@ -418,13 +418,13 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
         // One entry per non-empty group; the hits are unpacked by the select phase, whose loop runs at nearly full
         // lane occupancy. (Appending hit by hit here cost 27 % of the kernel's instructions at 6 active lanes of 32:
         // most lanes of a warp have no hit in a given group.)
-        if (m) {
-          const unsigned entry = ((unsigned)(enc + j + 1) << 16) | m;  // code of candidate j + i = (entry >> 16) + i (mod 2^16)
-          ent[min(ne, LP_ECAP)][tid] = entry;  // row LP_ECAP is never read
-          if (ne >= LP_ECAP) ovfE[min(ne - LP_ECAP, LP_EOVF - 1)] = entry;
-          ne++;
-          nh += __popc(m);
-        }
+        // Branch-free: every lane stores, a lane without a hit does not advance and overwrites the slot next time
+        // (as a predicated block this was 22 instructions at 9 active lanes in 85 % of the iterations).
+        const unsigned entry = ((unsigned)(enc + j) << 16) | m;
+        ent[min(ne, LP_ECAP)][tid] = entry;  // row LP_ECAP is never read
+        if (m != 0u && ne >= LP_ECAP) ovfE[min(ne - LP_ECAP, LP_EOVF - 1)] = entry;
+        ne += (m != 0u) ? 1 : 0;
+        nh += __popc(m);
       }
     }
     n = nh;
@@ -579,8 +579,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
   };
   // VAR 2: walk the hits of the entry list in scan order — a flat loop over the n hits (one per iteration for every
   // lane), fetching the next entry whenever the current mask is used up (entries are never empty)
-  // The sorted index of candidate i of an entry is (index of its first hit) + (i - i0): the cell number is decoded
-  // once per entry, from the code of its first HIT (the group's first candidate may lie in the cell before).
+  // The sorted index of candidate i of an entry is (index of the group's first candidate) + i, decoded once per entry.
   unsigned curMask = 0u;
   int curBase = 0, curEntry = 0;
   auto next_hit = [&]() -> int {
@@ -588,8 +587,11 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
       const unsigned e = (curEntry < LP_ECAP) ? ent[curEntry][tid] : ovfE[min(curEntry - LP_ECAP, LP_EOVF - 1)];
       curEntry++;
       curMask = e & 0xffffu;
-      const int i0 = __ffs(curMask) - 1;
-      curBase = hit_index(((e >> 16) + (unsigned)i0) & 0xffffu) - i0;
+#if SPH_LP_CBS
+      curBase = cbS[e >> 29][tid] + (int)((e >> 16) & 8191u) - 16;  // sorted index of the group's first candidate
+#else
+      curBase = cb[e >> 29] + (int)((e >> 16) & 8191u) - 16;
+#endif
     }
     const int i = __ffs(curMask) - 1;
     curMask &= curMask - 1u;
@@ -621,7 +623,7 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     for (int t = LP_CAP; t < n; t++) first_pass(hit_index(ovf[t - LP_CAP]), LpYes());
   }
   int jthr = SPH_RADIUS_SEGMENTS;  // radius threshold (sphFluid.cl:310-324)
-  {
+  if (within >= SPH_NB) {  // the bins hold at most `within` candidates: below 32 the running sum cannot reach 32
     int sum = 0;
     bool open = true;
 #pragma unroll
