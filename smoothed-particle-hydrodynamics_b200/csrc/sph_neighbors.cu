@@ -224,6 +224,12 @@ __global__ void __launch_bounds__(128) k_find_neighbors_generic(DevParams d, con
 #ifndef SPH_LP_PRMT
 #define SPH_LP_PRMT 1
 #endif
+#ifndef SPH_LP_WADDR
+#define SPH_LP_WADDR 1
+#endif
+#ifndef SPH_LP_BMSK
+#define SPH_LP_BMSK 1
+#endif
 
 
 // Sweep copy of the sorted positions: groups of 8 particles as (x[8] | y[8] | z[8]) = 96 bytes, so that the three
@@ -366,6 +372,11 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
     const __half2 nT = __float2half2_rn(-1.08984375f);
     const __half *Sh = reinterpret_cast<const __half *>(S);
     int nh = 0;
+#if SPH_LP_WADDR
+    // shared-memory address of this thread's next entry slot, kept in a register: recomputing it from threadIdx and
+    // the shared window base cost five instructions per iteration (the compiler rematerialises both at 48 registers)
+    const unsigned wAddr = (unsigned)__cvta_generic_to_shared(&ent[0][tid]);
+#endif
 #pragma unroll 1
     for (int k = 0; k < 8; k++) {
       const int b = cb[k], e = ce[k];
@@ -414,16 +425,30 @@ __global__ void __launch_bounds__(LP_THREADS, LP_MINB) k_find_neighbors_list(Dev
         // fold to 16 ascending bits; the group is aligned to 16: its ends may reach into the neighbouring cells
         m = (m & 0xffu) | ((m >> 8) & 0xff00u);
 #endif
+#if SPH_LP_BMSK
+        {  // candidates [max(b - j, 0), min(e - j, 16)) of the group belong to the cell: one bit-mask instruction
+          const int lo = max(b - j, 0);
+          unsigned vm;
+          asm("bmsk.clamp.b32 %0, %1, %2;" : "=r"(vm) : "r"(lo), "r"(min(e - j, 16) - lo));
+          m &= vm;
+        }
+#else
         m &= (0xffffu << max(b - j, 0)) & (0xffffu >> max(j + 16 - e, 0));
+#endif
         // One entry per non-empty group; the hits are unpacked by the select phase, whose loop runs at nearly full
         // lane occupancy. (Appending hit by hit here cost 27 % of the kernel's instructions at 6 active lanes of 32:
         // most lanes of a warp have no hit in a given group.)
         // Branch-free: every lane stores, a lane without a hit does not advance and overwrites the slot next time
         // (as a predicated block this was 22 instructions at 9 active lanes in 85 % of the iterations).
         const unsigned entry = ((unsigned)(enc + j) << 16) | m;
+#if SPH_LP_WADDR
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(wAddr + ((unsigned)min(ne, LP_ECAP) << 9)), "r"(entry) : "memory");  // row LP_ECAP is never read
+        static_assert(LP_THREADS * 4 == 512, "row stride of ent");
+#else
         ent[min(ne, LP_ECAP)][tid] = entry;  // row LP_ECAP is never read
-        if (m != 0u && ne >= LP_ECAP) ovfE[min(ne - LP_ECAP, LP_EOVF - 1)] = entry;
-        ne += (m != 0u) ? 1 : 0;
+#endif
+        if (__builtin_expect(m != 0u && ne >= LP_ECAP, 0)) ovfE[min(ne - LP_ECAP, LP_EOVF - 1)] = entry;
+        asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(ne) : "r"(m));  // ne += (m != 0)
         nh += __popc(m);
       }
     }
